@@ -1,0 +1,136 @@
+/* splat_b200 -- C ABI of the B200-native differentiable Gaussian-splat render.
+ *
+ * This is the drop-in boundary for the render path SplatFormer reaches through the
+ * gsplat v0.1.11 Python API.  The reference binds this path as a torch C++ extension
+ * (`gsplat.cuda._C`, loaded by `import gsplat` at /root/reference/utils/gs_utils.py:3);
+ * gsplat v0.1.11 itself is a pip-from-git dependency (/root/reference/README.md:27) that
+ * is not on disk, so each entry point below cites the reference CALL SITE it serves and
+ * the upstream binding name it stands in for.
+ *
+ * Conventions (all entry points)
+ *  - plain C: raw DEVICE pointers, sizes and scalars only; no torch types.
+ *  - asynchronous on `stream` (a cudaStream_t passed as void*); no host synchronisation,
+ *    no allocation, no ownership transfer, no global mutable state inside the library.
+ *    Scratch memory is supplied by the caller (`*_temp_bytes` tells how much).
+ *  - return value: 0 on success, otherwise a cudaError_t value (see sb_error_string);
+ *    negative values are argument errors detected on the host (SB_ERR_*).
+ *  - all float tensors are binary32, row-major, contiguous; ids/bins are int32, keys int64.
+ *  - every call is batched over `num_views` views that share the Gaussians and the image
+ *    size; the gsplat-compatible Python API calls with num_views = 1.  Per-view arrays are
+ *    laid out view-major: (V, N, ...), (V, H, W, ...), tile bins (V*T, 2).
+ *  - cameras: `viewmats` is (V, 3, 4) row-major world->camera (first 12 floats of a 3x4 or
+ *    4x4 matrix, stride `viewmat_stride` floats between views); `intrins` is (V, 4) =
+ *    fx, fy, cx, cy on the DEVICE, or NULL to use the scalar fx, fy, cx, cy arguments for
+ *    every view (what gsplat.project_gaussians receives at gs_utils.py:88-91).
+ */
+#ifndef SPLAT_B200_H_
+#define SPLAT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SB_ABI_VERSION 1
+#define SB_ERR_BAD_ARG (-1)
+#define SB_ERR_TEMP_TOO_SMALL (-2)
+
+typedef void* sb_stream_t; /* cudaStream_t */
+
+#if defined(__GNUC__)
+#define SB_API __attribute__((visibility("default")))
+#else
+#define SB_API
+#endif
+
+SB_API int sb_abi_version(void);
+SB_API const char* sb_error_string(int code);
+
+/* ---- a3 / a13: gsplat.spherical_harmonics (gs_utils.py:78) ---------------------------
+ * upstream bindings: _C.compute_sh_forward / _C.compute_sh_backward.
+ * dirs (V,N,3), coeffs (N,K,3) shared by all views, colors (V,N,3).
+ * `degree` is the storage degree (K = (degree+1)^2), `degrees_to_use` <= degree.
+ * backward: v_coeffs (N,K,3) = sum over views of Y_k(dir_v) * v_colors[v]; bases above
+ * degrees_to_use receive 0; no gradient to dirs. */
+SB_API int sb_sh_fwd(int num_views, int n, int degree, int degrees_to_use, const float* dirs,
+              const float* coeffs, float* colors, sb_stream_t stream);
+SB_API int sb_sh_bwd(int num_views, int n, int degree, int degrees_to_use, const float* dirs,
+              const float* v_colors, float* v_coeffs, sb_stream_t stream);
+
+/* ---- a4 / a12: gsplat.project_gaussians (gs_utils.py:82-95) ---------------------------
+ * upstream bindings: _C.project_gaussians_forward / _backward.
+ * Outputs (V,N,..): xys(2) depths radii(int) conics(3) compensation num_tiles_hit(int)
+ * cov3d(6); compensation and cov3d may be NULL (cov3d is written for the Gaussians in front
+ * of the view's near plane, also when they are culled later).
+ * Culled Gaussians get radii = num_tiles_hit = 0 and zeros elsewhere. */
+SB_API int sb_project_fwd(int num_views, int n, const float* means, const float* scales, float glob_scale,
+                   const float* quats, const float* viewmats, int viewmat_stride,
+                   const float* intrins, float fx, float fy, float cx, float cy, int img_h,
+                   int img_w, int block_width, float clip_thresh, float* xys, float* depths,
+                   int* radii, float* conics, float* compensation, int* num_tiles_hit,
+                   float* cov3d, sb_stream_t stream);
+/* v_* inputs are (V,N,..); v_depths, v_compensation and v_cov3d may be NULL.
+ * Outputs v_means (N,3), v_scales (N,3), v_quats (N,4) are the sums over views (assigned,
+ * not accumulated).  v_viewmats (V,3,4) may be NULL; if given it must be zero-filled by
+ * the caller and receives the pose gradient. */
+SB_API int sb_project_bwd(int num_views, int n, const float* means, const float* scales, float glob_scale,
+                   const float* quats, const float* viewmats, int viewmat_stride,
+                   const float* intrins, float fx, float fy, float cx, float cy, int img_h,
+                   int img_w, int block_width, float clip_thresh, const int* radii,
+                   const float* v_xys, const float* v_depths, const float* v_conics,
+                   const float* v_compensation, const float* v_cov3d, float* v_means,
+                   float* v_scales, float* v_quats, float* v_viewmats, sb_stream_t stream);
+
+/* ---- a5: gsplat.utils.compute_cumulative_intersects ------------------------------------
+ * inclusive int32 prefix sum over the flattened (V*N) tile counts. */
+SB_API size_t sb_cumsum_temp_bytes(int count);
+SB_API int sb_cumsum_i32(int count, const int* in, int* out, void* temp, size_t temp_bytes,
+                  sb_stream_t stream);
+
+/* ---- a6: gsplat.utils.map_gaussian_to_intersects (_C.map_gaussian_to_intersects) -------
+ * key = ((view*T + tile) << 32) | float32 bits of depth; gaussian_ids are view-local. */
+SB_API int sb_map_gaussian_to_intersects(int num_views, int n, const float* xys, const float* depths,
+                                  const int* radii, const int* cum_tiles_hit, int tiles_x,
+                                  int tiles_y, int block_width, int64_t* isect_ids,
+                                  int* gaussian_ids, sb_stream_t stream);
+
+/* ---- a7: the 64-bit (tile|depth) key sort (upstream: torch.sort + torch.gather) --------
+ * stable LSD radix sort of (key, value) pairs over key bits [0, end_bit). */
+SB_API size_t sb_sort_temp_bytes(int num_intersects);
+SB_API int sb_sort_pairs(int num_intersects, int end_bit, const int64_t* keys_in, const int* vals_in,
+                  int64_t* keys_out, int* vals_out, void* temp, size_t temp_bytes,
+                  sb_stream_t stream);
+
+/* ---- a8: gsplat.utils.get_tile_bin_edges (_C.get_tile_bin_edges) ------------------------
+ * tile_bins (num_tiles_total, 2) int32 must be zero-filled by the caller. */
+SB_API int sb_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted, int num_tiles_total,
+                      int* tile_bins, sb_stream_t stream);
+
+/* ---- a10 / a11: gsplat.rasterize_gaussians (gs_utils.py:96-109) -------------------------
+ * upstream bindings: _C.rasterize_forward / _C.rasterize_backward (3 channels).
+ * The kernels read one packed 48-byte record per (view, Gaussian):
+ *   [x, y, hx, hy | conic a, b, c, opacity | r, g, b, 0]   (hx, hy: conservative half
+ *   extents of the region where alpha >= 1/255, used only to skip work)
+ * built from the API tensors by sb_pack_splats.  Gradients come back in a packed
+ * 48-byte record [v_x, v_y, v_ca, v_cb | v_cc, v_opacity, v_r, v_g | v_b, 0, 0, 0] that
+ * the caller zero-fills; sb_unpack_splat_grads splits it into API tensors. */
+SB_API int sb_pack_splats(int count, const float* xys, const float* conics, const float* colors,
+                   const float* opacity, float* packed, sb_stream_t stream);
+SB_API int sb_rasterize_fwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
+                     const int* tile_bins, const float* background, int img_h, int img_w,
+                     int block_width, float* out_img, float* final_ts, int* final_idx,
+                     sb_stream_t stream);
+SB_API int sb_rasterize_bwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
+                     const int* tile_bins, const float* background, int img_h, int img_w,
+                     int block_width, const float* final_ts, const int* final_idx,
+                     const float* v_out_img, const float* v_out_alpha, float* v_packed,
+                     sb_stream_t stream);
+SB_API int sb_unpack_splat_grads(int count, const float* v_packed, float* v_xys, float* v_conics,
+                          float* v_colors, float* v_opacity, sb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPLAT_B200_H_ */

@@ -1,0 +1,63 @@
+// ABI bookkeeping + the small layout kernels around the rasteriser.
+#include "sb_common.cuh"
+
+namespace sb {
+
+__global__ void __launch_bounds__(256) pack_kernel(int count, const float* __restrict__ xys,
+                                                   const float* __restrict__ conics,
+                                                   const float* __restrict__ colors,
+                                                   const float* __restrict__ opacity,
+                                                   float4* __restrict__ packed) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= count) return;
+  const float2 c = __ldg(reinterpret_cast<const float2*>(xys) + i);
+  const float ka = __ldg(conics + 3 * i), kb = __ldg(conics + 3 * i + 1), kc = __ldg(conics + 3 * i + 2);
+  const float op = __ldg(opacity + i);
+  float hx, hy;
+  visible_extent(ka, kb, kc, op, hx, hy);
+  packed[3 * i] = make_float4(c.x, c.y, hx, hy);
+  packed[3 * i + 1] = make_float4(ka, kb, kc, op);
+  packed[3 * i + 2] = make_float4(__ldg(colors + 3 * i), __ldg(colors + 3 * i + 1), __ldg(colors + 3 * i + 2), 0.f);
+}
+
+__global__ void __launch_bounds__(256) unpack_grads_kernel(int count, const float4* __restrict__ vp,
+                                                           float* __restrict__ v_xys,
+                                                           float* __restrict__ v_conics,
+                                                           float* __restrict__ v_colors,
+                                                           float* __restrict__ v_opacity) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= count) return;
+  const float4 a = __ldg(vp + 3 * i), b = __ldg(vp + 3 * i + 1), c = __ldg(vp + 3 * i + 2);
+  reinterpret_cast<float2*>(v_xys)[i] = make_float2(a.x, a.y);
+  v_conics[3 * i] = a.z; v_conics[3 * i + 1] = a.w; v_conics[3 * i + 2] = b.x;
+  v_opacity[i] = b.y;
+  v_colors[3 * i] = b.z; v_colors[3 * i + 1] = b.w; v_colors[3 * i + 2] = c.x;
+}
+
+}  // namespace sb
+
+extern "C" int sb_abi_version(void) { return SB_ABI_VERSION; }
+
+extern "C" const char* sb_error_string(int code) {
+  if (code == SB_ERR_BAD_ARG) return "splat_b200: invalid argument";
+  if (code == SB_ERR_TEMP_TOO_SMALL) return "splat_b200: scratch buffer too small";
+  return cudaGetErrorString((cudaError_t)code);
+}
+
+extern "C" int sb_pack_splats(int count, const float* xys, const float* conics, const float* colors,
+                              const float* opacity, float* packed, sb_stream_t stream) {
+  if (count < 0) return SB_ERR_BAD_ARG;
+  if (count == 0) return 0;
+  sb::pack_kernel<<<sb::ceil_div(count, 256), 256, 0, (cudaStream_t)stream>>>(
+      count, xys, conics, colors, opacity, reinterpret_cast<float4*>(packed));
+  SB_RETURN_LAST();
+}
+
+extern "C" int sb_unpack_splat_grads(int count, const float* v_packed, float* v_xys, float* v_conics,
+                                     float* v_colors, float* v_opacity, sb_stream_t stream) {
+  if (count < 0) return SB_ERR_BAD_ARG;
+  if (count == 0) return 0;
+  sb::unpack_grads_kernel<<<sb::ceil_div(count, 256), 256, 0, (cudaStream_t)stream>>>(
+      count, reinterpret_cast<const float4*>(v_packed), v_xys, v_conics, v_colors, v_opacity);
+  SB_RETURN_LAST();
+}

@@ -1,0 +1,92 @@
+"""Tiling helpers with the names and return values of gsplat.utils in v0.1.11, which
+`gsplat.rasterize_gaussians` (call site /root/reference/utils/gs_utils.py:96-109) is built from.
+Each one is a thin wrapper over the C ABI (include/splat_b200.h rows a5-a9)."""
+from __future__ import annotations
+
+from typing import Tuple
+
+import torch
+from torch import Tensor
+
+from . import _abi
+
+
+def _scratch(nbytes: int, device) -> Tensor:
+    return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)
+
+
+def compute_cumulative_intersects(num_tiles_hit: Tensor) -> Tuple[int, Tensor]:
+    """Inclusive int32 prefix sum of the per-Gaussian tile counts and its last element.
+    The `.item()` is the one host synchronisation upstream has here as well."""
+    lib = _abi.load()
+    flat = num_tiles_hit.contiguous().view(-1)
+    cum = torch.empty_like(flat)
+    n = flat.numel()
+    if n == 0:
+        return 0, cum
+    tmp = _scratch(lib.sb_cumsum_temp_bytes(n), flat.device)
+    _abi.check(lib.sb_cumsum_i32(n, _abi.ptr(flat, torch.int32, "num_tiles_hit"),
+                                 _abi.ptr(cum, torch.int32, "cum_tiles_hit"),
+                                 _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()),
+               "sb_cumsum_i32")
+    return int(cum[-1].item()), cum
+
+
+def map_gaussian_to_intersects(num_points: int, num_intersects: int, xys: Tensor, depths: Tensor,
+                               radii: Tensor, cum_tiles_hit: Tensor, tile_bounds, block_width: int,
+                               num_views: int = 1) -> Tuple[Tensor, Tensor]:
+    lib = _abi.load()
+    dev = xys.device
+    isect_ids = torch.empty(num_intersects, dtype=torch.int64, device=dev)
+    gaussian_ids = torch.empty(num_intersects, dtype=torch.int32, device=dev)
+    _abi.check(lib.sb_map_gaussian_to_intersects(
+        num_views, num_points, _abi.ptr(xys.contiguous(), torch.float32, "xys"),
+        _abi.ptr(depths.contiguous(), torch.float32, "depths"),
+        _abi.ptr(radii.contiguous(), torch.int32, "radii"),
+        _abi.ptr(cum_tiles_hit.contiguous(), torch.int32, "cum_tiles_hit"),
+        int(tile_bounds[0]), int(tile_bounds[1]), block_width,
+        _abi.ptr(isect_ids, torch.int64, "isect_ids"), _abi.ptr(gaussian_ids, torch.int32, "gaussian_ids"),
+        _abi.stream()), "sb_map_gaussian_to_intersects")
+    return isect_ids, gaussian_ids
+
+
+def sort_isects(isect_ids: Tensor, gaussian_ids: Tensor, num_tiles_total: int) -> Tuple[Tensor, Tensor]:
+    """Ascending stable sort of the 64-bit (tile|depth) keys carrying the Gaussian ids."""
+    lib = _abi.load()
+    n = isect_ids.numel()
+    keys_out = torch.empty_like(isect_ids)
+    vals_out = torch.empty_like(gaussian_ids)
+    if n == 0:
+        return keys_out, vals_out
+    end_bit = 32 + max(1, (max(num_tiles_total, 1) - 1).bit_length())
+    tmp = _scratch(lib.sb_sort_temp_bytes(n), isect_ids.device)
+    _abi.check(lib.sb_sort_pairs(n, end_bit, _abi.ptr(isect_ids, torch.int64, "isect_ids"),
+                                 _abi.ptr(gaussian_ids, torch.int32, "gaussian_ids"),
+                                 _abi.ptr(keys_out, torch.int64, "isect_ids_sorted"),
+                                 _abi.ptr(vals_out, torch.int32, "gaussian_ids_sorted"),
+                                 _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()),
+               "sb_sort_pairs")
+    return keys_out, vals_out
+
+
+def get_tile_bin_edges(num_intersects: int, isect_ids_sorted: Tensor, tile_bounds,
+                       num_views: int = 1) -> Tensor:
+    lib = _abi.load()
+    tiles = int(tile_bounds[0]) * int(tile_bounds[1]) * num_views
+    tile_bins = torch.zeros(tiles, 2, dtype=torch.int32, device=isect_ids_sorted.device)
+    _abi.check(lib.sb_tile_bin_edges(num_intersects, _abi.ptr(isect_ids_sorted, torch.int64, "isect_ids_sorted"),
+                                     tiles, _abi.ptr(tile_bins, torch.int32, "tile_bins"), _abi.stream()),
+               "sb_tile_bin_edges")
+    return tile_bins
+
+
+def bin_and_sort_gaussians(num_points: int, num_intersects: int, xys: Tensor, depths: Tensor,
+                           radii: Tensor, cum_tiles_hit: Tensor, tile_bounds, block_width: int,
+                           num_views: int = 1):
+    """-> (isect_ids_unsorted, gaussian_ids_unsorted, isect_ids_sorted, gaussian_ids_sorted, tile_bins)"""
+    isect_ids, gaussian_ids = map_gaussian_to_intersects(
+        num_points, num_intersects, xys, depths, radii, cum_tiles_hit, tile_bounds, block_width, num_views)
+    tiles = int(tile_bounds[0]) * int(tile_bounds[1]) * num_views
+    isect_ids_sorted, gaussian_ids_sorted = sort_isects(isect_ids, gaussian_ids, tiles)
+    tile_bins = get_tile_bin_edges(num_intersects, isect_ids_sorted, tile_bounds, num_views)
+    return isect_ids, gaussian_ids, isect_ids_sorted, gaussian_ids_sorted, tile_bins

@@ -1,0 +1,80 @@
+"""Shared test utilities: the wrapper logic of the reference's render call on a pluggable backend,
+comparison helpers and small scene builders."""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from oracle import ref_torch as R
+from splatformer_b200 import synth
+
+IMG_ATOL = 1e-4        # north_star: rendered RGB / alpha within 1e-4 absolute
+GRAD_RTOL = 1e-3       # north_star: per-Gaussian gradients within 1e-3 relative
+FRAGILE_MARGIN = 2e-5  # pixels whose alpha>=1/255, T<=1e-4 or 0.999-clamp decision is this close to
+                       # its threshold (relative) are set aside: the decision is a discontinuity and
+                       # flips with the last bits of exp()
+
+
+def activated(gs, device=None, dtype=torch.float32):
+    """Raw SplatFormer parameters -> the tensors the three gsplat calls receive."""
+    means = gs["means"].to(dtype)
+    scales = torch.exp(gs["scales"].to(dtype))
+    quats = gs["quats"].to(dtype)
+    quats = quats / quats.norm(dim=-1, keepdim=True)
+    opac = torch.sigmoid(gs["opacities"].to(dtype))
+    coeffs = gs["features_dc"].to(dtype).unsqueeze(1)
+    if "features_rest" in gs:
+        coeffs = torch.cat([coeffs, gs["features_rest"].to(dtype)], dim=1)
+    out = dict(means=means, scales=scales, quats=quats, opacities=opac, coeffs=coeffs)
+    if device is not None:
+        out = {k: v.to(device) for k, v in out.items()}
+    return out
+
+
+def cam_scalars(cams):
+    return dict(fx=float(cams["fx"]), fy=float(cams["fy"]), cx=float(cams["cx"]), cy=float(cams["cy"]),
+                H=int(cams["height"]), W=int(cams["width"]))
+
+
+def view_inputs(gs, cams, view=0, device=None, dtype=torch.float32):
+    """Everything one per-view pass needs: activated params, viewmat (3x4), unit viewdirs, colours path."""
+    a = activated(gs, None, dtype)
+    c2w = cams["camera_to_worlds"][view]
+    vm = R.viewmat_from_c2w(c2w)[:3, :].contiguous().to(dtype)
+    dirs = a["means"] - c2w[:3, 3].to(dtype)
+    dirs = dirs / dirs.norm(dim=-1, keepdim=True)
+    a.update(viewmat=vm, viewdirs=dirs, background=cams["background_color"].to(dtype))
+    if device is not None:
+        a = {k: v.to(device) for k, v in a.items()}
+    return a
+
+
+def colors_from(backend, inp, degree):
+    if degree == 0:
+        return torch.sigmoid(inp["coeffs"][:, 0, :])
+    return torch.clamp(backend.spherical_harmonics(degree, inp["viewdirs"], inp["coeffs"]) + 0.5, min=0.0)
+
+
+def rel_l2(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def assert_grad_close(got, ref, name, rtol=GRAD_RTOL):
+    """|got - ref| <= rtol * |ref| + rtol * rms(ref) elementwise, and relative L2 error <= rtol."""
+    got, ref = got.double().cpu(), ref.double().cpu()
+    assert got.shape == ref.shape, (name, got.shape, ref.shape)
+    rms = float(ref.pow(2).mean().sqrt())
+    err = (got - ref).abs()
+    bound = rtol * ref.abs() + rtol * rms
+    bad = err > bound
+    assert not bool(bad.any()), (f"{name}: {int(bad.sum())} of {bad.numel()} elements off; worst err "
+                                 f"{float(err.max()):.3e}, rms(ref) {rms:.3e}")
+    assert rel_l2(got, ref) <= rtol, f"{name}: relative L2 error {rel_l2(got, ref):.3e}"
+
+
+def small_scene(n=600, deg=2, seed=7, size=64, views=2, scale_mult=0.6):
+    gs = synth.shell_scene(n, deg, seed=seed, scale_mult=scale_mult)
+    cams = synth.orbit_cameras(views, size, size, background=(0.1, 0.2, 0.3))
+    return gs, cams

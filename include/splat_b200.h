@@ -115,13 +115,16 @@ SB_API int sb_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted
  *   extents of the region where alpha >= 1/255, used only to skip work)
  * built from the API tensors by sb_pack_splats.  Gradients come back in a packed
  * 48-byte record [v_x, v_y, v_ca, v_cb | v_cc, v_opacity, v_r, v_g | v_b, 0, 0, 0] that
- * the caller zero-fills; sb_unpack_splat_grads splits it into API tensors. */
+ * the caller zero-fills; sb_unpack_splat_grads splits it into API tensors.
+ * cum_tiles_hit (V*N inclusive scan, may be NULL): when given, a view without a single
+ * intersection gets out_img = background and final_T = 0 (alpha 1) -- the behaviour of
+ * upstream's `num_intersects < 1` early return, applied per view on the device. */
 SB_API int sb_pack_splats(int count, const float* xys, const float* conics, const float* colors,
                    const float* opacity, float* packed, sb_stream_t stream);
 SB_API int sb_rasterize_fwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
                      const int* tile_bins, const float* background, int img_h, int img_w,
-                     int block_width, float* out_img, float* final_ts, int* final_idx,
-                     sb_stream_t stream);
+                     int block_width, const int* cum_tiles_hit, float* out_img, float* final_ts,
+                     int* final_idx, sb_stream_t stream);
 SB_API int sb_rasterize_bwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
                      const int* tile_bins, const float* background, int img_h, int img_w,
                      int block_width, const float* final_ts, const int* final_idx,
@@ -129,6 +132,31 @@ SB_API int sb_rasterize_bwd(int num_views, int n, const float* packed, const int
                      sb_stream_t stream);
 SB_API int sb_unpack_splat_grads(int count, const float* v_packed, float* v_xys, float* v_conics,
                           float* v_colors, float* v_opacity, sb_stream_t stream);
+
+/* ---- a1 / a2: fused multi-view projection + SH colour ----------------------------------
+ * The view loop of rasterize_gaussians_to_multiimgs (gs_utils.py:20-27) with the per-view
+ * colour path of gs_utils.py:64-79 folded in; one launch for all V views of a scene.
+ *   sh_degree = -1: color_src is (N,3) view-independent rgb (degree-0 path, gs_utils.py:65)
+ *   sh_degree 0..4: color_src is (N,K,3) SH coefficients, colour = max(SH(mean - campos_v) + 0.5, 0)
+ * opacities (N,) are activated values; campos (V,3) camera centres (may be NULL if sh_degree=-1).
+ * Writes the packed raster record (V,N,12) for drawn Gaussians, depths/radii/num_tiles_hit
+ * (V,N) for all.  The backward consumes the packed gradient record of sb_rasterize_bwd and
+ * writes the per-Gaussian sums over views: v_means (N,3) v_scales (N,3) v_quats (N,4)
+ * v_opacities (N,) and v_color_src (same shape as color_src). */
+SB_API int sb_views_project_fwd(int num_views, int n, const float* means, const float* scales,
+                         float glob_scale, const float* quats, const float* opacities,
+                         const float* color_src, int sh_degree, const float* viewmats,
+                         int viewmat_stride, const float* intrins, float fx, float fy, float cx,
+                         float cy, const float* campos, int img_h, int img_w, int block_width,
+                         float clip_thresh, float* packed, float* depths, int* radii,
+                         int* num_tiles_hit, sb_stream_t stream);
+SB_API int sb_views_project_bwd(int num_views, int n, const float* means, const float* scales,
+                         float glob_scale, const float* quats, int sh_degree, const float* viewmats,
+                         int viewmat_stride, const float* intrins, float fx, float fy, float cx,
+                         float cy, const float* campos, int img_h, int img_w, int block_width,
+                         float clip_thresh, const float* packed, const float* v_packed,
+                         float* v_means, float* v_scales, float* v_quats, float* v_opacities,
+                         float* v_color_src, sb_stream_t stream);
 
 #ifdef __cplusplus
 }

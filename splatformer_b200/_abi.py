@@ -33,10 +33,15 @@ SIGNATURES = {
     "sb_sort_pairs": (I, [I, I, P, P, P, P, P, S, P]),
     "sb_tile_bin_edges": (I, [I, P, I, P, P]),
     "sb_pack_splats": (I, [I, P, P, P, P, P, P]),
-    "sb_rasterize_fwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P]),
+    "sb_rasterize_fwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P]),
     "sb_rasterize_bwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, P]),
     "sb_unpack_splat_grads": (I, [I, P, P, P, P, P, P]),
+    "sb_views_project_fwd": (I, [I, I, P, P, F, P, P, P, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P, P]),
+    "sb_views_project_bwd": (I, [I, I, P, P, F, P, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P, P, P, P, P]),
 }
+
+# number of ABI calls that enqueued device work since import (bench.py reports it as gpu_launches)
+LAUNCHES = 0
 
 
 def lib_path() -> str:
@@ -63,6 +68,8 @@ def load() -> ctypes.CDLL:
 
 
 def check(code: int, what: str) -> None:
+    global LAUNCHES
+    LAUNCHES += 1
     if code != 0:
         msg = load().sb_error_string(code).decode()
         raise RuntimeError(f"{what} failed: {msg} (code {code})")

@@ -189,7 +189,7 @@ class _RasterizeGaussians(Function):
         _abi.check(lib.sb_rasterize_fwd(
             1, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
             _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
-            img_width, block_width, _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
+            img_width, block_width, None, _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
             _abi.ptr(final_idx, I32, "final_idx"), _abi.stream()), "sb_rasterize_fwd")
         ctx.empty = False
         ctx.num_intersects = num_intersects

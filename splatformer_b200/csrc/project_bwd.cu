@@ -2,7 +2,7 @@
 // reference call site /root/reference/utils/gs_utils.py:82-95).  One thread per Gaussian walks
 // the views, recomputes the forward record (cheaper than storing ~50 floats per view) and sums
 // the per-view VJPs in registers, so v_means / v_scales / v_quats are written once.
-#include "sb_common.cuh"
+#include "sh_stage.cuh"
 
 namespace sb {
 
@@ -91,6 +91,80 @@ __global__ void __launch_bounds__(kProjBwdBlock) project_bwd_kernel(
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Fused multi-view backward: counterpart of views_project_fwd_kernel.  Reads the packed gradient
+// record [v_x v_y v_ca v_cb | v_cc v_op v_r v_g | v_b ...] the raster backward accumulated for
+// every (view, Gaussian), recomputes the forward record (this TU is built with --fmad=false like
+// the forward, so `valid` is reproduced exactly), and sums over the views in registers:
+// v_means, v_scales, v_quats, v_opacities and v_coeffs (or v_rgb) are each written once.
+// ------------------------------------------------------------------------------------------------
+constexpr int kViewsBwdBlock = 128;
+
+template <int DEG>
+__global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
+    int num_views, int n, const float* __restrict__ means, const float* __restrict__ scales, float glob,
+    const float* __restrict__ quats, CamSrc cams, const float* __restrict__ campos, int img_h, int img_w,
+    int bw, float clip, int k3_store, const float4* __restrict__ packed,
+    const float4* __restrict__ v_packed, float* __restrict__ v_means, float* __restrict__ v_scales,
+    float* __restrict__ v_quats, float* __restrict__ v_opacities, float* __restrict__ v_color_src) {
+  extern __shared__ float smem[];
+  constexpr int KU = DEG < 0 ? 1 : (DEG + 1) * (DEG + 1);
+  const int g0 = blockIdx.x * kViewsBwdBlock;
+  const int nb = min(kViewsBwdBlock, n - g0);
+  const int g = g0 + threadIdx.x;
+  const bool active = threadIdx.x < nb;
+  float acc[KU * 3];
+#pragma unroll
+  for (int i = 0; i < KU * 3; ++i) acc[i] = 0.f;
+  if (active) {
+    const float m[3] = {__ldg(means + 3 * g), __ldg(means + 3 * g + 1), __ldg(means + 3 * g + 2)};
+    const float s[3] = {__ldg(scales + 3 * g), __ldg(scales + 3 * g + 1), __ldg(scales + 3 * g + 2)};
+    const float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
+    const float q[4] = {q4.x, q4.y, q4.z, q4.w};
+    float am[3] = {0, 0, 0}, as[3] = {0, 0, 0}, aq[4] = {0, 0, 0, 0}, aop = 0.f;
+    for (int v = 0; v < num_views; ++v) {
+      const Cam cam = load_cam(cams, v);
+      ProjFwd f;
+      project_fwd_one(m, s, glob, q, cam, img_w, img_h, bw, clip, f);
+      if (!f.valid) continue;
+      const size_t i = (size_t)v * n + g;
+      const float4 ga = __ldg(v_packed + 3 * i), gb = __ldg(v_packed + 3 * i + 1), gc = __ldg(v_packed + 3 * i + 2);
+      float vm[3], vs[3], vq[4];
+      project_bwd_one(m, s, glob, cam, f, ga.x, ga.y, 0.f, ga.z, ga.w, gb.x, 0.f, nullptr, vm, vs, vq, nullptr);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { am[k] += vm[k]; as[k] += vs[k]; }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) aq[k] += vq[k];
+      aop += gb.y;
+      float vr = gb.z, vg = gb.w, vb = gc.x;
+      if (DEG >= 0) {
+        const float4 col = __ldg(packed + 3 * i + 2);      // clamp(x + 0.5, min 0): gradient passes where > 0
+        vr = col.x > 0.f ? vr : 0.f; vg = col.y > 0.f ? vg : 0.f; vb = col.z > 0.f ? vb : 0.f;
+        float Y[KU];
+        sh_basis(DEG, m[0] - __ldg(campos + 3 * v), m[1] - __ldg(campos + 3 * v + 1), m[2] - __ldg(campos + 3 * v + 2), Y);
+#pragma unroll
+        for (int k = 0; k < KU; ++k) { acc[3 * k] += Y[k] * vr; acc[3 * k + 1] += Y[k] * vg; acc[3 * k + 2] += Y[k] * vb; }
+      } else {
+        acc[0] += vr; acc[1] += vg; acc[2] += vb;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { v_means[3 * g + k] = am[k]; v_scales[3 * g + k] = as[k]; }
+    reinterpret_cast<float4*>(v_quats)[g] = make_float4(aq[0], aq[1], aq[2], aq[3]);
+    v_opacities[g] = aop;
+    if (DEG < 0) { v_color_src[3 * g] = acc[0]; v_color_src[3 * g + 1] = acc[1]; v_color_src[3 * g + 2] = acc[2]; }
+  }
+  if (DEG >= 0) {
+    const int row = padded_row(k3_store);
+    if (active) {
+#pragma unroll
+      for (int i = 0; i < KU * 3; ++i) smem[threadIdx.x * row + i] = acc[i];
+    }
+    __syncthreads();
+    stage_rows_out(smem, v_color_src + (size_t)g0 * k3_store, nb, k3_store, kViewsBwdBlock);
+  }
+}
+
 }  // namespace sb
 
 extern "C" int sb_project_bwd(int num_views, int n, const float* means, const float* scales,
@@ -114,5 +188,35 @@ extern "C" int sb_project_bwd(int num_views, int n, const float* means, const fl
     sb::project_bwd_kernel<false><<<grid, sb::kProjBwdBlock, 0, st>>>(
         num_views, n, means, scales, glob_scale, quats, cams, img_h, img_w, block_width, clip_thresh,
         radii, v_xys, v_depths, v_conics, v_compensation, v_cov3d, v_means, v_scales, v_quats, nullptr);
+  SB_RETURN_LAST();
+}
+
+extern "C" int sb_views_project_bwd(int num_views, int n, const float* means, const float* scales,
+                                    float glob_scale, const float* quats, int sh_degree,
+                                    const float* viewmats, int viewmat_stride, const float* intrins,
+                                    float fx, float fy, float cx, float cy, const float* campos,
+                                    int img_h, int img_w, int block_width, float clip_thresh,
+                                    const float* packed, const float* v_packed, float* v_means,
+                                    float* v_scales, float* v_quats, float* v_opacities,
+                                    float* v_color_src, sb_stream_t stream) {
+  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || sh_degree < -1 || sh_degree > 4 ||
+      (sh_degree >= 0 && !campos))
+    return SB_ERR_BAD_ARG;
+  if (n == 0) return 0;
+  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy};
+  const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
+  const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsBwdBlock * (k3 | 1) * sizeof(float);
+  dim3 grid(sb::ceil_div(n, sb::kViewsBwdBlock));
+  cudaStream_t st = (cudaStream_t)stream;
+  const float4* pk = reinterpret_cast<const float4*>(packed);
+  const float4* vpk = reinterpret_cast<const float4*>(v_packed);
+#define SB_CASE(D)                                                                                   \
+  case D:                                                                                            \
+    sb::views_project_bwd_kernel<D><<<grid, sb::kViewsBwdBlock, smem, st>>>(                         \
+        num_views, n, means, scales, glob_scale, quats, cams, campos, img_h, img_w, block_width,     \
+        clip_thresh, k3, pk, vpk, v_means, v_scales, v_quats, v_opacities, v_color_src);             \
+    break;
+  switch (sh_degree) { SB_CASE(-1) SB_CASE(0) SB_CASE(1) SB_CASE(2) SB_CASE(3) SB_CASE(4) }
+#undef SB_CASE
   SB_RETURN_LAST();
 }

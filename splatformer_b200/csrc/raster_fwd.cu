@@ -13,8 +13,8 @@ namespace sb {
 __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ ids_sorted,
     const int2* __restrict__ tile_bins, const float* __restrict__ background, int tiles_x,
-    int tiles_y, int img_w, int img_h, int bw, float* __restrict__ out_img,
-    float* __restrict__ final_ts, int* __restrict__ final_idx) {
+    int tiles_y, int img_w, int img_h, int bw, const int* __restrict__ cum_tiles_hit,
+    float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx) {
   __shared__ float4 sA[kBatch], sB[kBatch], sC[kBatch];
   const int tile = blockIdx.x, v = blockIdx.y;
   const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
@@ -67,6 +67,18 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
   }
   if (pm.inside) {
     const size_t pix = ((size_t)v * img_h + pm.py_i) * img_w + pm.px_i;
+    if (cum_tiles_hit) {
+      // upstream quirk: a view without a single intersection reports final_T = 0
+      // (alpha = 1) while its image is the plain background
+      const int hi = __ldg(cum_tiles_hit + (size_t)(v + 1) * n - 1);
+      const int lo = v ? __ldg(cum_tiles_hit + (size_t)v * n - 1) : 0;
+      if (hi - lo < 1) {
+        final_ts[pix] = 0.f; final_idx[pix] = 0;
+        out_img[3 * pix] = __ldg(background); out_img[3 * pix + 1] = __ldg(background + 1);
+        out_img[3 * pix + 2] = __ldg(background + 2);
+        return;
+      }
+    }
     final_ts[pix] = T;
     final_idx[pix] = cur_idx;
     out_img[3 * pix] = pr + T * __ldg(background);
@@ -80,7 +92,8 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
 extern "C" int sb_rasterize_fwd(int num_views, int n, const float* packed,
                                 const int* gaussian_ids_sorted, const int* tile_bins,
                                 const float* background, int img_h, int img_w, int block_width,
-                                float* out_img, float* final_ts, int* final_idx, sb_stream_t stream) {
+                                const int* cum_tiles_hit, float* out_img, float* final_ts,
+                                int* final_idx, sb_stream_t stream) {
   if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || block_width < 2 || block_width > 16)
     return SB_ERR_BAD_ARG;
   const int tiles_x = sb::ceil_div(img_w, block_width), tiles_y = sb::ceil_div(img_h, block_width);
@@ -88,6 +101,6 @@ extern "C" int sb_rasterize_fwd(int num_views, int n, const float* packed,
   sb::raster_fwd_kernel<<<grid, sb::kRasterBlock, 0, (cudaStream_t)stream>>>(
       n, reinterpret_cast<const float4*>(packed), gaussian_ids_sorted,
       reinterpret_cast<const int2*>(tile_bins), background, tiles_x, tiles_y, img_w, img_h, block_width,
-      out_img, final_ts, final_idx);
+      cum_tiles_hit, out_img, final_ts, final_idx);
   SB_RETURN_LAST();
 }

@@ -5,7 +5,7 @@
 // Gaussian reading its own row would issue stride-(12K)-byte requests.  Instead a block moves
 // its 128 rows (one contiguous span of global memory) through shared memory with float4
 // accesses and the threads read/write their row from a padded (conflict-free) shared layout.
-#include "sb_common.cuh"
+#include "sh_stage.cuh"
 
 namespace sb {
 
@@ -18,29 +18,10 @@ __global__ void __launch_bounds__(kShBlock) sh_fwd_kernel(int num_views, int n, 
                                                           float* __restrict__ colors) {
   extern __shared__ float smem[];
   constexpr int KU = (DEG + 1) * (DEG + 1);
-  const int row = k3_store | 1;  // odd row stride: conflict-free per-thread rows
+  const int row = padded_row(k3_store);
   const int g0 = blockIdx.x * kShBlock;
   const int nb = min(kShBlock, n - g0);
-  const size_t base = (size_t)g0 * k3_store;
-  const int total = nb * k3_store;
-  // cooperative load; base*4 bytes is 16-byte aligned because kShBlock*k3_store*4 % 16 == 0
-  const float4* src4 = reinterpret_cast<const float4*>(coeffs + base);
-  const int total4 = total >> 2;
-  for (int i = threadIdx.x; i < total4; i += kShBlock) {
-    const float4 v = __ldg(src4 + i);
-    int e = i << 2;
-    int g = e / k3_store, k = e - g * k3_store;
-    const float vals[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      smem[g * row + k] = vals[j];
-      if (++k == k3_store) { k = 0; ++g; }
-    }
-  }
-  for (int e = (total4 << 2) + threadIdx.x; e < total; e += kShBlock) {
-    const int g = e / k3_store, k = e - g * k3_store;
-    smem[g * row + k] = __ldg(coeffs + base + e);
-  }
+  stage_rows_in(smem, coeffs + (size_t)g0 * k3_store, nb, k3_store, kShBlock);
   __syncthreads();
   const int g = g0 + threadIdx.x;
   if (threadIdx.x >= nb) return;
@@ -66,7 +47,7 @@ __global__ void __launch_bounds__(kShBlock) sh_bwd_kernel(int num_views, int n, 
                                                           float* __restrict__ v_coeffs) {
   extern __shared__ float smem[];
   constexpr int KU = (DEG + 1) * (DEG + 1);
-  const int row = k3_store | 1;  // odd row stride: conflict-free per-thread rows
+  const int row = padded_row(k3_store);
   const int g0 = blockIdx.x * kShBlock;
   const int nb = min(kShBlock, n - g0);
   const int g = g0 + threadIdx.x;
@@ -87,25 +68,7 @@ __global__ void __launch_bounds__(kShBlock) sh_bwd_kernel(int num_views, int n, 
     for (int i = KU * 3; i < k3_store; ++i) smem[threadIdx.x * row + i] = 0.f;
   }
   __syncthreads();
-  const size_t base = (size_t)g0 * k3_store;
-  const int total = nb * k3_store;
-  float4* dst4 = reinterpret_cast<float4*>(v_coeffs + base);
-  const int total4 = total >> 2;
-  for (int i = threadIdx.x; i < total4; i += kShBlock) {
-    int e = i << 2;
-    int gq = e / k3_store, k = e - gq * k3_store;
-    float vals[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      vals[j] = smem[gq * row + k];
-      if (++k == k3_store) { k = 0; ++gq; }
-    }
-    dst4[i] = make_float4(vals[0], vals[1], vals[2], vals[3]);
-  }
-  for (int e = (total4 << 2) + threadIdx.x; e < total; e += kShBlock) {
-    const int gq = e / k3_store, k = e - gq * k3_store;
-    v_coeffs[base + e] = smem[gq * row + k];
-  }
+  stage_rows_out(smem, v_coeffs + (size_t)g0 * k3_store, nb, k3_store, kShBlock);
 }
 
 template <bool FWD>

@@ -1,0 +1,207 @@
+"""Fused multi-view render: all V views of a scene in one pass per stage.
+
+This is the B200-native form of the loop SplatFormer runs in
+`rasterize_gaussians_to_multiimgs` (/root/reference/utils/gs_utils.py:20-27): instead of V times
+(SH, project, cumsum + .item(), emit, sort, bins, rasterise) -- about ten launches and nine host
+synchronisations per view -- every stage is launched once for the whole (V, N) / (V, H, W) batch
+through the C ABI, view-independent data (SH coefficients, Gaussian parameters) is read from HBM
+once per scene, and the per-Gaussian gradients are summed over the views in registers.
+Results are the ones the per-view gsplat-compatible API (`splatformer_b200.api`) produces: the
+same device functions run underneath.
+"""
+from __future__ import annotations
+
+import contextlib
+from typing import Dict, List, Optional, Tuple
+
+import torch
+from torch import Tensor
+from torch.autograd import Function
+
+from . import _abi, utils
+
+F32, I32 = torch.float32, torch.int32
+
+
+class StageTimer:
+    """CUDA-event timing of the individual ABI calls (used by bench.py for the roofline of the
+    dominant kernel).  Events are recorded on the current stream around each stage."""
+
+    def __init__(self):
+        self.events: List[Tuple[str, torch.cuda.Event, torch.cuda.Event]] = []
+
+    @contextlib.contextmanager
+    def stage(self, name: str):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        yield
+        b.record()
+        self.events.append((name, a, b))
+
+    def totals_ms(self) -> Dict[str, float]:
+        torch.cuda.synchronize()
+        out: Dict[str, float] = {}
+        for name, a, b in self.events:
+            out[name] = out.get(name, 0.0) + a.elapsed_time(b)
+        return out
+
+    def counts(self) -> Dict[str, int]:
+        out: Dict[str, int] = {}
+        for name, _, _ in self.events:
+            out[name] = out.get(name, 0) + 1
+        return out
+
+
+_timer: Optional[StageTimer] = None
+
+
+@contextlib.contextmanager
+def profile_stages():
+    """with profile_stages() as t: ...render...; t.totals_ms()"""
+    global _timer
+    prev, _timer = _timer, StageTimer()
+    try:
+        yield _timer
+    finally:
+        _timer = prev
+
+
+def _stage(name: str):
+    return _timer.stage(name) if _timer is not None else contextlib.nullcontext()
+
+
+def _c(t: Tensor) -> Tensor:
+    return _abi.aligned16(t.contiguous())
+
+
+class _RenderViews(Function):
+    @staticmethod
+    def forward(ctx, means, scales, quats, opacities, color_src, viewmats, campos, intrins, sh_degree,
+                img_height, img_width, block_width, background, clip_thresh):
+        lib = _abi.load()
+        dev = means.device
+        n = means.shape[0]
+        v = viewmats.shape[0]
+        means, scales, quats = _c(means), _c(scales), _c(quats)
+        opacities = _c(opacities).view(-1)
+        color_src = _c(color_src)
+        viewmats = _c(viewmats.to(F32))
+        vm_stride = viewmats.shape[1] * viewmats.shape[2]
+        campos = _c(campos.to(F32))
+        intrins = _c(intrins.to(F32))
+        background = _c(background.to(F32))
+        tiles_x = (img_width + block_width - 1) // block_width
+        tiles_y = (img_height + block_width - 1) // block_width
+
+        packed = torch.empty(v, n, 12, dtype=F32, device=dev)
+        depths = torch.empty(v, n, dtype=F32, device=dev)
+        radii = torch.empty(v, n, dtype=I32, device=dev)
+        tiles_hit = torch.empty(v, n, dtype=I32, device=dev)
+        with _stage("project_sh_fwd"):
+            _abi.check(lib.sb_views_project_fwd(
+                v, n, _abi.ptr(means, F32, "means"), _abi.ptr(scales, F32, "scales"), 1.0,
+                _abi.ptr(quats, F32, "quats"), _abi.ptr(opacities, F32, "opacities"),
+                _abi.ptr(color_src, F32, "color_src"), sh_degree, _abi.ptr(viewmats, F32, "viewmats"),
+                vm_stride, _abi.ptr(intrins, F32, "intrins"), 0.0, 0.0, 0.0, 0.0,
+                _abi.ptr(campos, F32, "campos"), img_height, img_width, block_width, clip_thresh,
+                _abi.ptr(packed, F32, "packed"), _abi.ptr(depths, F32, "depths"),
+                _abi.ptr(radii, I32, "radii"), _abi.ptr(tiles_hit, I32, "num_tiles_hit"), _abi.stream()),
+                "sb_views_project_fwd")
+        with _stage("cumsum"):
+            num_intersects, cum = utils.compute_cumulative_intersects(tiles_hit)
+        out_img = torch.empty(v, img_height, img_width, 3, dtype=F32, device=dev)
+        final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
+        final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)
+        with _stage("map_isect"):
+            isect_ids, gaussian_ids = _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x,
+                                           tiles_y, block_width)
+        with _stage("sort"):
+            isect_sorted, gids_sorted = utils.sort_isects(isect_ids, gaussian_ids, tiles_x * tiles_y * v)
+        with _stage("bin_edges"):
+            tile_bins = utils.get_tile_bin_edges(num_intersects, isect_sorted, (tiles_x, tiles_y, 1), v)
+        with _stage("raster_fwd"):
+            _abi.check(lib.sb_rasterize_fwd(
+                v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
+                _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
+                img_width, block_width, _abi.ptr(cum, I32, "cum_tiles_hit"), _abi.ptr(out_img, F32, "out_img"),
+                _abi.ptr(final_ts, F32, "final_Ts"),
+                _abi.ptr(final_idx, I32, "final_idx"), _abi.stream()), "sb_rasterize_fwd")
+        ctx.meta = (v, n, sh_degree, img_height, img_width, block_width, clip_thresh, vm_stride,
+                    tuple(color_src.shape), num_intersects)
+        ctx.save_for_backward(means, scales, quats, viewmats, campos, intrins, background, packed,
+                              gids_sorted, tile_bins, final_ts, final_idx)
+        ctx.set_materialize_grads(False)
+        return out_img, 1 - final_ts
+
+    @staticmethod
+    def backward(ctx, v_out_img, v_out_alpha):
+        lib = _abi.load()
+        (means, scales, quats, viewmats, campos, intrins, background, packed, gids_sorted, tile_bins,
+         final_ts, final_idx) = ctx.saved_tensors
+        (v, n, sh_degree, img_height, img_width, block_width, clip_thresh, vm_stride, color_shape,
+         num_intersects) = ctx.meta
+        dev = means.device
+        if v_out_img is None and v_out_alpha is None:
+            return (None,) * 14
+        v_out_img = torch.zeros(v, img_height, img_width, 3, dtype=F32, device=dev) if v_out_img is None \
+            else _c(v_out_img)
+        v_out_alpha = None if v_out_alpha is None else _c(v_out_alpha)
+        with _stage("zero_grads"):
+            v_packed = torch.zeros(v, n, 12, dtype=F32, device=dev)
+        with _stage("raster_bwd"):
+            _abi.check(lib.sb_rasterize_bwd(
+                v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
+                _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
+                img_width, block_width, _abi.ptr(final_ts, F32, "final_Ts"),
+                _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(v_out_img, F32, "v_out_img"),
+                _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(v_packed, F32, "v_packed"),
+                _abi.stream()), "sb_rasterize_bwd")
+        v_means = torch.empty(n, 3, dtype=F32, device=dev)
+        v_scales = torch.empty(n, 3, dtype=F32, device=dev)
+        v_quats = torch.empty(n, 4, dtype=F32, device=dev)
+        v_opac = torch.empty(n, 1, dtype=F32, device=dev)
+        v_color = torch.empty(color_shape, dtype=F32, device=dev)
+        with _stage("project_sh_bwd"):
+            _abi.check(lib.sb_views_project_bwd(
+                v, n, _abi.ptr(means, F32, "means"), _abi.ptr(scales, F32, "scales"), 1.0,
+                _abi.ptr(quats, F32, "quats"), sh_degree, _abi.ptr(viewmats, F32, "viewmats"), vm_stride,
+                _abi.ptr(intrins, F32, "intrins"), 0.0, 0.0, 0.0, 0.0, _abi.ptr(campos, F32, "campos"),
+                img_height, img_width, block_width, clip_thresh, _abi.ptr(packed, F32, "packed"),
+                _abi.ptr(v_packed, F32, "v_packed"), _abi.ptr(v_means, F32, "v_means"),
+                _abi.ptr(v_scales, F32, "v_scales"), _abi.ptr(v_quats, F32, "v_quats"),
+                _abi.ptr(v_opac, F32, "v_opacities"), _abi.ptr(v_color, F32, "v_color_src"), _abi.stream()),
+                "sb_views_project_bwd")
+        return (v_means, v_scales, v_quats, v_opac, v_color, None, None, None, None, None, None, None, None,
+                None)
+
+
+def _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x, tiles_y, block_width):
+    """Key emission for the batched path reads pixel centres straight from the packed record
+    (stride 12 floats) -- the ABI's map function takes contiguous (V*N, 2) xys, so gather them."""
+    xys = packed.view(v * n, 12)[:, :2].contiguous()
+    return utils.map_gaussian_to_intersects(n, num_intersects, xys, depths.view(-1), radii.view(-1), cum,
+                                            (tiles_x, tiles_y, 1), block_width, num_views=v)
+
+
+def render_views(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor, color_src: Tensor,
+                 sh_degree: int, viewmats: Tensor, campos: Optional[Tensor], intrins: Tensor,
+                 img_height: int, img_width: int, block_width: int = 16,
+                 background: Optional[Tensor] = None, clip_thresh: float = 0.01):
+    """Render all V views of one scene.
+
+    means (N,3), scales (N,3, activated), quats (N,4, unit), opacities (N,1|N, activated);
+    color_src: (N,K,3) SH coefficients with sh_degree in 0..4 (colour = max(SH + 0.5, 0) as
+    gs_utils.py:78-79) or (N,3) rgb with sh_degree = -1; viewmats (V,3|4,4) world->camera;
+    campos (V,3) camera centres; intrins (V,4) = fx, fy, cx, cy.
+    Returns rgb (V,H,W,3) (not clamped) and alpha (V,H,W).  Differentiable in means, scales, quats,
+    opacities and color_src."""
+    assert 2 <= block_width <= 16, "block_width must be between 2 and 16"
+    if not means.is_cuda:
+        raise RuntimeError("render_views needs CUDA tensors (there is no CPU path)")
+    if background is None:
+        background = torch.ones(3, dtype=F32, device=means.device)
+    if campos is None:
+        campos = torch.zeros(viewmats.shape[0], 3, dtype=F32, device=means.device)
+    return _RenderViews.apply(means, scales, quats, opacities, color_src, viewmats, campos, intrins,
+                              int(sh_degree), int(img_height), int(img_width), int(block_width), background,
+                              float(clip_thresh))

@@ -1,0 +1,101 @@
+"""The fused multi-view path (splatformer_b200.render / gs_utils) against the per-view
+gsplat-compatible API and against the oracle's wrapper."""
+import pytest
+import torch
+
+import gsplat
+from oracle import ref_torch as R
+from splatformer_b200 import gs_utils, synth
+import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+
+def _per_view_api(raw, cams, view, deg, cuda):
+    """rasterize_gaussians_to_singleimg logic on the per-view API (three gsplat calls)."""
+    k = H.cam_scalars(cams)
+    c2w = cams["camera_to_worlds"][view].to(cuda)
+    vm = gs_utils.viewmats_from_c2w(c2w[None])[0][0]       # same world->camera bits as the fused path
+    scales = torch.exp(raw["scales"])
+    quats = raw["quats"] / raw["quats"].norm(dim=-1, keepdim=True)
+    opac = torch.sigmoid(raw["opacities"])
+    if deg == 0:
+        rgbs = torch.sigmoid(raw["features_dc"])
+    else:
+        coeffs = torch.cat([raw["features_dc"].unsqueeze(1), raw["features_rest"]], dim=1)
+        dirs = raw["means"].detach() - c2w[:3, 3]
+        dirs = dirs / dirs.norm(dim=-1, keepdim=True)
+        rgbs = torch.clamp(gsplat.spherical_harmonics(deg, dirs, coeffs) + 0.5, min=0.0)
+    xys, depths, radii, conics, comp, tiles, cov3d = gsplat.project_gaussians(
+        raw["means"], scales, 1, quats, vm, k["fx"], k["fy"], k["cx"], k["cy"], k["H"], k["W"], 16)
+    rgb, alpha = gsplat.rasterize_gaussians(xys, depths, radii, conics, tiles, rgbs, opac, k["H"], k["W"], 16,
+                                            background=cams["background_color"].to(cuda), return_alpha=True)
+    return torch.clamp(rgb, max=1.0), alpha.unsqueeze(-1)
+
+
+@pytest.mark.parametrize("n,deg,size,views", [(3000, 3, (160, 128), 3), (2500, 0, (96, 96), 2),
+                                              (1500, 1, (72, 100), 4)])
+def test_fused_matches_per_view_api(cuda, sb_lib, n, deg, size, views):
+    gs = synth.shell_scene(n, deg, seed=21, scale_mult=0.3)
+    cams = synth.orbit_cameras(views, size[0], size[1], background=(0.3, 0.1, 0.2))
+    gt = synth.target_images(views, size[1], size[0], seed=4).to(cuda)
+    raw_a = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    raw_b = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    cams_dev = {k_: v.to(cuda) for k_, v in cams.items()}
+    rgbs, alphas = gs_utils.rasterize_gaussians_to_multiimgs(raw_a, cams_dev)
+    assert len(rgbs) == views and rgbs[0].shape == (size[1], size[0], 3) and alphas[0].shape == (size[1], size[0], 1)
+    loss_a = sum((rgbs[v] - gt[v]).abs().mean() + 0.1 * alphas[v].mean() for v in range(views))
+    loss_b = 0.0
+    for v in range(views):
+        rgb, alpha = _per_view_api(raw_b, cams, v, deg, cuda)
+        # forward: same device functions underneath; alpha is bit-identical, colours differ only by
+        # where the view direction is normalised (torch outside vs once inside the fused kernel)
+        assert torch.equal(alpha, alphas[v]), f"view {v}: fused alpha differs from per-view API"
+        assert float((rgb - rgbs[v]).abs().max()) <= 2e-6
+        loss_b = loss_b + (rgb - gt[v]).abs().mean() + 0.1 * alpha.mean()
+    loss_a.backward()
+    loss_b.backward()
+    for name in gs:
+        H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name, rtol=1e-4)
+
+
+def test_fused_matches_oracle_wrapper(cuda, sb_lib):
+    gs = synth.shell_scene(2000, 2, seed=33, scale_mult=0.3)
+    cams = synth.orbit_cameras(2, 112, 96, background=(0.0, 0.0, 0.0))
+    raw = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    raw_ref = {k_: v.clone().requires_grad_() for k_, v in gs.items()}
+    rgbs, alphas = gs_utils.rasterize_gaussians_to_multiimgs(raw, {k_: v.to(cuda) for k_, v in cams.items()})
+    loss, loss_ref = 0.0, 0.0
+    gt = synth.target_images(2, 96, 112, seed=8)
+    for v in range(2):
+        rgb_ref, a_ref, aux = R.render_view(raw_ref, cams["camera_to_worlds"][v], cams["cx"], cams["cy"],
+                                            cams["fx"], cams["fy"], cams["width"], cams["height"],
+                                            cams["background_color"], return_aux=True)
+        solid = aux["margin"] > H.FRAGILE_MARGIN
+        err = (rgbs[v].detach().cpu() - rgb_ref.detach()).abs().amax(-1)
+        assert float(err[solid].max()) <= H.IMG_ATOL
+        assert float((alphas[v].detach().cpu() - a_ref.detach()).abs()[solid].max()) <= H.IMG_ATOL
+        m = solid[..., None].float()
+        loss_ref = loss_ref + ((rgb_ref - gt[v]).abs() * m).mean()
+        loss = loss + ((rgbs[v] - gt[v].to(cuda)).abs() * m.to(cuda)).mean()
+    loss.backward(); loss_ref.backward()
+    for name in gs:
+        H.assert_grad_close(raw[name].grad, raw_ref[name].grad, name, rtol=5e-3)
+
+
+def test_fused_single_view_and_empty_view(cuda, sb_lib):
+    gs = synth.shell_scene(500, 1, seed=2, scale_mult=0.3)
+    cams = synth.orbit_cameras(2, 64, 64, background=(0.5, 0.25, 0.125))
+    # second camera looks away from the object: nothing intersects -> background, alpha 1 (A.5 quirk)
+    away = cams["camera_to_worlds"][1].clone()
+    away[:3, :3] = away[:3, :3] @ torch.diag(torch.tensor([-1.0, 1.0, -1.0]))
+    cams["camera_to_worlds"][1] = away
+    raw = {k_: v.to(cuda) for k_, v in gs.items()}
+    cd = {k_: v.to(cuda) for k_, v in cams.items()}
+    rgbs, alphas = gs_utils.rasterize_gaussians_to_multiimgs(raw, cd)
+    assert torch.allclose(rgbs[1], cd["background_color"].expand(64, 64, 3))
+    assert bool((alphas[1] == 1).all())
+    assert float(alphas[0].mean()) > 0.05
+    rgb0, a0 = gs_utils.rasterize_gaussians_to_singleimg(raw, cd["camera_to_worlds"][0], **{
+        k_: cd[k_] for k_ in ("cx", "cy", "fx", "fy", "width", "height", "background_color")})
+    assert torch.equal(rgb0, rgbs[0]) and torch.equal(a0, alphas[0])

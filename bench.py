@@ -1,0 +1,410 @@
+#!/usr/bin/env python
+"""bench.py -- forward+backward splat-render throughput on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A *step* is one pass of the hot path over one scene: forward + backward of the render loss
+`mean(abs(rgb - gt))` (/root/reference/train.py:273-275,289) over all V views of a
+100k-Gaussian / SH3 / 512x512 scene (BASELINE.json configs[1]), through the drop-in wrapper
+`rasterize_gaussians_to_multiimgs` (/root/reference/utils/gs_utils.py:20).
+
+  value   whole-job Mpix/s with the scene, cameras and targets already resident in HBM
+          (CUDA events, barrier + synchronize on both sides, max over ranks)
+  e2e     the same metric with HOST (pinned) inputs: every step copies the raw Gaussian
+          parameters, cameras and target images host->device, renders fwd+bwd through the
+          same public call and reads the loss back
+  roofline   dominant kernel: algorithmic bytes per launch / its mean CUDA-event
+             duration inside the timed region, against MEASURED_PEAKS.json
+  cpu_baseline   the oracle (pure-PyTorch port of the reference path) on the host cores,
+                 on a bounded sample (a few views of the same scene)
+
+N > 1 (torchrun, one rank per GPU): scene-sharded as SplatFormer's DDP does (one scene per GPU
+per step, /root/reference/dataset/Loader.py:15-17): no data-path collective, weak scaling.
+`--shard view` splits every scene's views over the ranks instead and all-reduces the packed
+per-Gaussian gradients over NCCL (strong scaling per scene).
+
+`--impl reference` times the reference's CPU implementation of the path (the oracle port: gsplat
+v0.1.11 is not on disk) on rank 0's host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "Mpix/s fwd+bwd splat render (100k Gauss, SH3, 512^2)"
+UNIT = "Mpix/s"
+WORKLOAD = "objaverse_100k_sh3_512"
+
+
+def _env_int(name: str, default: int) -> int:
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def stage_bytes_per_view(n: int, k: int, isect: float, pix: int, tiles: int) -> dict:
+    """Algorithmic (compulsory) bytes per view and stage, SURVEY.md 8(d)."""
+    return {
+        "project_sh_fwd": (12 * k + 24) * n + 100 * n,
+        "cumsum": 8 * n,
+        "map_isect": 20 * n + 12 * isect,
+        "sort": 24 * isect,
+        "bin_edges": 8 * isect + 8 * tiles,
+        "raster_fwd": 4 * isect + 36 * n + 20 * pix,
+        "raster_bwd": 4 * isect + 72 * n + 24 * pix,
+        "project_sh_bwd": 152 * n + (12 * k + 24) * n,
+    }
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed regions run."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,utilization.gpu,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int):
+        self.proc = None
+        self.path = None
+        try:
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            ident = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+        except Exception:
+            ident = str(device_index)
+        fd, self.path = tempfile.mkstemp(prefix="clocks_", suffix=".csv")
+        os.close(fd)
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={ident}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "50"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self) -> dict:
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons, busy = [], [], set(), []
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 8:
+                    continue
+                try:
+                    clk, mx = float(f[0]), float(f[1])
+                except ValueError:
+                    continue
+                try:
+                    util = float(f[3])
+                except ValueError:
+                    util = 100.0
+                sm.append(clk)
+                smax.append(mx)
+                if util > 0:
+                    busy.append(clk)
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"),
+                                     f[4:8]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+        finally:
+            try:
+                os.unlink(self.path)
+            except OSError:
+                pass
+        use = busy or sm
+        if use:
+            out.update(sm_mhz=statistics.median(use), sm_max_mhz=max(smax), reasons=sorted(reasons),
+                       samples=len(use))
+        return out
+
+
+def run_reference(args, rank: int) -> None:
+    """Reference arm: the reference's CPU implementation of the path (oracle port), rank 0 only."""
+    if rank != 0:
+        return
+    from oracle import ref_torch as R
+    from splatformer_b200 import synth
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    views = max(1, args.ref_views)
+    gs, cams, gt = synth.make_config(WORKLOAD, 0)
+    c = synth.CONFIGS[WORKLOAD]
+    sample_cams = dict(cams)
+    # evenly spaced subset of the 32 views = the bounded sample
+    idx = torch.linspace(0, c["views"] - 1, views).round().long()
+    sample_cams["camera_to_worlds"] = cams["camera_to_worlds"][idx]
+    gt_s = gt[idx]
+
+    def step():
+        raw = {k: v.clone().requires_grad_() for k, v in gs.items()}
+        rgbs, _ = R.render_views(raw, sample_cams)
+        loss = sum((rgb - g).abs().mean() for rgb, g in zip(rgbs, gt_s)) / views
+        loss.backward()
+        return float(loss.detach())
+
+    for _ in range(args.warmup_ref):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps_ref):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps_ref
+    pix = views * c["height"] * c["width"]
+    val = pix / dt / 1e6
+    sample = f"{views} of {c['views']} views of the scene per step (fwd+bwd), {args.steps_ref} steps"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps_ref, "warmup": args.warmup_ref, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "gaussians": c["n"], "sh_degree": c["deg"], "views": c["views"],
+                   "image": [c["height"], c["width"]], "sample_views_per_step": views},
+        "gaussians_per_s": views * c["n"] / dt,
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(views: int) -> dict:
+    from oracle import ref_torch as R
+    from splatformer_b200 import synth
+    cores = os.cpu_count() or 1
+    prev = torch.get_num_threads()
+    torch.set_num_threads(cores)
+    try:
+        gs, cams, gt = synth.make_config(WORKLOAD, 0)
+        c = synth.CONFIGS[WORKLOAD]
+        idx = torch.linspace(0, c["views"] - 1, views).round().long()
+        sample_cams = dict(cams)
+        sample_cams["camera_to_worlds"] = cams["camera_to_worlds"][idx]
+        raw = {k: v.clone().requires_grad_() for k, v in gs.items()}
+        t0 = time.perf_counter()
+        rgbs, _ = R.render_views(raw, sample_cams)
+        loss = sum((rgb - g).abs().mean() for rgb, g in zip(rgbs, gt[idx])) / views
+        loss.backward()
+        dt = time.perf_counter() - t0
+    finally:
+        torch.set_num_threads(prev)
+    return {"value": views * c["height"] * c["width"] / dt / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{views} of {c['views']} views of the same scene, fwd+bwd once, oracle/ref_torch.py",
+            "seconds": dt}
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--shard", default="scene", choices=["scene", "view"])
+    ap.add_argument("--views", type=int, default=None, help="override the views per scene (default: config's 32)")
+    ap.add_argument("--cpu-views", type=int, default=3, help="views of the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--ref-views", type=int, default=2)
+    ap.add_argument("--steps-ref", type=int, default=None)
+    ap.add_argument("--warmup-ref", type=int, default=None)
+    args = ap.parse_args()
+
+    rank = _env_int("RANK", 0)
+    local_rank = _env_int("LOCAL_RANK", 0)
+    world = _env_int("WORLD_SIZE", 1)
+
+    if args.impl == "reference":
+        # the CPU path costs ~5 s per view: bound the run irrespective of the GPU arm's K / W
+        args.steps_ref = args.steps_ref if args.steps_ref is not None else max(1, min(args.steps, 3))
+        args.warmup_ref = args.warmup_ref if args.warmup_ref is not None else min(args.warmup, 1)
+        run_reference(args, rank)
+        return
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the renderer has no CPU path "
+                         "(use --impl reference for the CPU reference arm)")
+    if args.warmup < 3:
+        args.warmup = 3
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    from splatformer_b200 import _abi, gs_utils, render, synth
+    from splatformer_b200 import dist as sbdist
+    _abi.load()
+
+    c = synth.CONFIGS[WORKLOAD]
+    n, deg, H, W = c["n"], c["deg"], c["height"], c["width"]
+    V = args.views or c["views"]
+    K = (deg + 1) ** 2
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+
+    # ---- inputs: NSCENE distinct scenes per rank, rotated between steps (inputs > L2) --------
+    NSCENE = 2
+    scenes = []
+    view_lo, view_hi = 0, V
+    if args.shard == "view" and world > 1:
+        view_lo, view_hi = sbdist.view_slice(V, rank, world)
+    for s in range(NSCENE):
+        sid = (s if args.shard == "view" else rank * NSCENE + s)
+        gs, cams, gt = synth.make_config(WORKLOAD, sid, num_views=V)
+        cams = dict(cams)
+        cams["camera_to_worlds"] = cams["camera_to_worlds"][view_lo:view_hi].contiguous()
+        gt = gt[view_lo:view_hi].contiguous()
+        scenes.append((gs, cams, gt))
+    v_local = view_hi - view_lo
+    norm = 1.0 / (V * H * W * 3)            # mean over all V views of the scene, also when view-sharded
+
+    host = [({k: v.pin_memory() for k, v in gs.items()}, {k: v.pin_memory() for k, v in cams.items()},
+             gt.pin_memory()) for gs, cams, gt in scenes]
+    resident = [({k: v.to(dev).requires_grad_() for k, v in gs.items()}, {k: v.to(dev) for k, v in cams.items()},
+                 gt.to(dev)) for gs, cams, gt in scenes]
+    h2d_bytes = sum(v.numel() * v.element_size() for v in host[0][0].values()) \
+        + sum(v.numel() * v.element_size() for v in host[0][1].values()) \
+        + host[0][2].numel() * host[0][2].element_size()
+
+    def render_loss(raw, cams, gt):
+        rgbs, _ = gs_utils.rasterize_gaussians_to_multiimgs(raw, cams)
+        rgb = torch.stack(rgbs, 0)
+        return (rgb - gt).abs().sum() * norm
+
+    def sync_grads(raw):
+        if args.shard == "view" and world > 1:
+            sbdist.allreduce_gaussian_grads(raw)
+
+    def step_resident(i):
+        raw, cams, gt = resident[i % NSCENE]
+        for p in raw.values():
+            p.grad = None
+        loss = render_loss(raw, cams, gt)
+        loss.backward()
+        sync_grads(raw)
+        return loss
+
+    def step_e2e(i):
+        hgs, hcams, hgt = host[i % NSCENE]
+        raw = {k: v.to(dev, non_blocking=True).requires_grad_() for k, v in hgs.items()}
+        cams = {k: v.to(dev, non_blocking=True) for k, v in hcams.items()}
+        gt = hgt.to(dev, non_blocking=True)
+        loss = render_loss(raw, cams, gt)
+        loss.backward()
+        sync_grads(raw)
+        return float(loss.item())          # device->host read of the step's result
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, with_stages=False):
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        launches0 = _abi.LAUNCHES
+        stage_ms, stage_calls = {}, {}
+        ctx = render.profile_stages() if with_stages else None
+        timer = ctx.__enter__() if ctx else None
+        a.record()
+        for i in range(steps):
+            fn(i)
+        b.record()
+        barrier()
+        if ctx:
+            stage_ms, stage_calls = timer.totals_ms(), timer.counts()
+            ctx.__exit__(None, None, None)
+        ms = a.elapsed_time(b)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, _abi.LAUNCHES - launches0, stage_ms, stage_calls
+
+    for i in range(args.warmup):
+        step_resident(i)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ms_total, launches, stage_ms, stage_calls = timed(step_resident, args.steps, with_stages=True)
+    isect_per_view = render.last_num_intersects() / max(v_local, 1)
+
+    e2e = None
+    if not args.no_e2e:
+        for i in range(3):
+            step_e2e(i)
+        e2e_ms, _, _, _ = timed(step_e2e, args.steps)
+    clocks = sampler.stop() if sampler else None
+
+    if rank == 0:
+        ms_step = ms_total / args.steps
+        scenes_per_step = world if args.shard == "scene" else 1
+        pix_step = scenes_per_step * V * H * W
+        value = pix_step / (ms_step * 1e-3) / 1e6
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"
+        per_view = stage_bytes_per_view(n, K, isect_per_view, H * W, tiles)
+        top = max(stage_ms, key=stage_ms.get) if stage_ms else None
+        roofline = None
+        stages = {}
+        for name, tot in stage_ms.items():
+            calls = max(stage_calls.get(name, 1), 1)
+            avg_ms = tot / calls
+            entry = {"ms_per_launch": avg_ms, "share_of_step": tot / ms_total}
+            if name in per_view:
+                gbs = per_view[name] * v_local / (avg_ms * 1e-3) / 1e9
+                entry.update(alg_bytes_per_launch=per_view[name] * v_local, gbs=gbs, frac=gbs / peak)
+            stages[name] = entry
+        if top and top in per_view:
+            roofline = {"kernel": top, "bound": "hbm", "achieved": stages[top]["gbs"], "peak": peak, "unit": "GB/s",
+                        "frac": stages[top]["frac"], "traffic": None, "peak_source": peak_src,
+                        "alg_bytes_per_launch": stages[top]["alg_bytes_per_launch"],
+                        "ms_per_launch": stages[top]["ms_per_launch"], "views_per_launch": v_local}
+        b_alg_view = sum(per_view.values())
+        step_gbs = b_alg_view * v_local / (ms_step * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak" if args.shard == "scene" else "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "gaussians": n, "sh_degree": deg, "views": V, "image": [H, W],
+                       "scenes_per_step": scenes_per_step, "sharding": args.shard if world > 1 else "single",
+                       "l2": f"inputs rotate over {NSCENE} scenes per rank ({NSCENE * h2d_bytes / 1e6:.0f} MB) and "
+                             "the per-step working set (~0.6 GB) exceeds the 126 MB L2",
+                       "intersections_per_view": isect_per_view},
+            "gaussians_per_s": scenes_per_step * V * n / (ms_step * 1e-3),
+            "hbm_frac_step": {"alg_bytes_per_view": b_alg_view, "gbs": step_gbs, "frac": step_gbs / peak,
+                              "peak": peak, "peak_source": peak_src},
+            "roofline": roofline, "stages": stages, "gpu_launches": launches, "clocks": clocks,
+        }
+        if not args.no_e2e:
+            e2e_step = e2e_ms / args.steps
+            line["e2e"] = {"value": pix_step / (e2e_step * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_step,
+                           "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4,
+                           "api": "splatformer_b200.gs_utils.rasterize_gaussians_to_multiimgs + L1 loss + backward"}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args.cpu_views)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

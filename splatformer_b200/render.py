@@ -53,6 +53,12 @@ class StageTimer:
 
 
 _timer: Optional[StageTimer] = None
+_last_num_intersects = 0
+
+
+def last_num_intersects() -> int:
+    """Intersections (over all views) of the most recent render_views call (bench.py reports it)."""
+    return _last_num_intersects
 
 
 @contextlib.contextmanager
@@ -109,6 +115,8 @@ class _RenderViews(Function):
                 "sb_views_project_fwd")
         with _stage("cumsum"):
             num_intersects, cum = utils.compute_cumulative_intersects(tiles_hit)
+        global _last_num_intersects
+        _last_num_intersects = num_intersects
         out_img = torch.empty(v, img_height, img_width, 3, dtype=F32, device=dev)
         final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
         final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)

@@ -1,0 +1,99 @@
+"""The vectorised oracle (masked cumprod + autograd) against the literal per-pixel loops of
+oracle/ref_loop.py (sequential walk, hand-derived reverse walk) and against float64 finite
+differences.  Two independent statements of SURVEY.md A.5/A.6 must agree."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_loop as L
+from oracle import ref_torch as R
+from splatformer_b200 import synth
+import helpers as H
+
+
+def _projected(n, size, seed, bw=16, mult=0.6, dtype=torch.float64):
+    gs = synth.shell_scene(n, 0, seed=seed, scale_mult=mult)
+    cams = synth.orbit_cameras(1, size[0], size[1], background=(0.2, 0.3, 0.1))
+    k = H.cam_scalars(cams)
+    inp = H.view_inputs(gs, cams, 0)
+    with torch.no_grad():
+        xys, depths, radii, conics, comp, tiles, cov3d = R.project_gaussians(
+            inp["means"], inp["scales"], 1, inp["quats"], inp["viewmat"], k["fx"], k["fy"], k["cx"], k["cy"],
+            k["H"], k["W"], bw)
+    colors = torch.sigmoid(inp["coeffs"][:, 0, :])
+    return (xys.to(dtype), depths, radii, conics.to(dtype), tiles, colors.to(dtype), inp["opacities"].to(dtype),
+            inp["background"].to(dtype), k)
+
+
+@pytest.mark.parametrize("n,size,bw,seed", [(60, (32, 32), 16, 1), (150, (40, 24), 16, 2), (80, (30, 30), 12, 3)])
+def test_vectorised_oracle_matches_pixel_loop(n, size, bw, seed):
+    xys, depths, radii, conics, tiles, colors, opac, bg, k = _projected(n, size, seed, bw)
+    leaves = [t.clone().requires_grad_() for t in (xys, conics, colors, opac)]
+    img, alpha, aux = R.rasterize_gaussians(leaves[0], depths, radii, leaves[1], tiles, leaves[2], leaves[3],
+                                            k["H"], k["W"], bw, background=bg, return_alpha=True, return_aux=True)
+    assert aux["num_intersects"] > n // 2
+    torch.manual_seed(seed)
+    v_img = torch.randn(img.shape, dtype=torch.float64)
+    v_alpha = torch.randn(alpha.shape, dtype=torch.float64)
+    ((img * v_img).sum() + (alpha * v_alpha).sum()).backward()
+    res = L.rasterize_loop(xys.numpy(), conics.numpy(), colors.numpy(), opac.numpy(),
+                           aux["gaussian_ids_sorted"].numpy(), aux["tile_bins"].numpy(), k["H"], k["W"], bw,
+                           bg.numpy(), v_out_img=v_img.numpy(), v_out_alpha=v_alpha.numpy())
+    assert np.allclose(res["out_img"], img.detach().numpy(), atol=1e-12)
+    assert np.allclose(res["out_alpha"], alpha.detach().numpy(), atol=1e-12)
+    assert np.array_equal(res["final_idx"], aux["final_idx"].numpy())
+    for name, leaf, key in (("v_xy", leaves[0], "v_xy"), ("v_conic", leaves[1], "v_conic"),
+                            ("v_colors", leaves[2], "v_colors")):
+        assert np.allclose(res[key], leaf.grad.numpy(), rtol=1e-9, atol=1e-12), name
+    assert np.allclose(res["v_opacity"], leaves[3].grad.numpy().reshape(-1), rtol=1e-9, atol=1e-12)
+
+
+def test_projection_gradients_match_finite_differences():
+    torch.manual_seed(0)
+    n = 6
+    gs = synth.shell_scene(n, 0, seed=4, scale_mult=3.0)
+    cams = synth.orbit_cameras(1, 64, 48)
+    k = H.cam_scalars(cams)
+    inp = H.view_inputs(gs, cams, 0, dtype=torch.float64)
+
+    def fn(means, scales, quats, viewmat):
+        xys, depths, radii, conics, comp, tiles, cov3d = R.project_gaussians(
+            means, scales, 1, quats, viewmat, k["fx"], k["fy"], k["cx"], k["cy"], k["H"], k["W"], 16)
+        assert int((radii > 0).sum()) == n
+        return xys, depths, conics, comp, cov3d
+
+    args = [inp[x].clone().requires_grad_() for x in ("means", "scales", "quats", "viewmat")]
+    assert torch.autograd.gradcheck(fn, args, eps=1e-6, atol=1e-5, rtol=1e-4, nondet_tol=0.0)
+
+
+def test_raster_gradients_match_finite_differences():
+    xys, depths, radii, conics, tiles, colors, opac, bg, k = _projected(25, (32, 32), 9, mult=2.0)
+    # keep every decision away from its threshold so that finite differences see a smooth function
+    opac = opac.clamp(0.05, 0.6)
+
+    def fn(xy, con, col, op):
+        img, alpha, aux = R.rasterize_gaussians(xy, depths, radii, con, tiles, col, op, k["H"], k["W"], 16,
+                                                background=bg, return_alpha=True, return_aux=True)
+        mask = (aux["margin"] > 1e-3).to(img.dtype)
+        return (img * mask[..., None]).sum(dim=(0, 1)), (alpha * mask).sum()
+
+    args = [t.clone().requires_grad_() for t in (xys, conics, colors, opac)]
+    assert torch.autograd.gradcheck(fn, args, eps=1e-7, atol=1e-5, rtol=1e-3, nondet_tol=0.0)
+
+
+def test_wrapper_matches_manual_three_calls():
+    gs = synth.shell_scene(400, 2, seed=12, scale_mult=0.6)
+    cams = synth.orbit_cameras(2, 48, 40, background=(0.3, 0.2, 0.1))
+    k = H.cam_scalars(cams)
+    rgbs, alphas = R.render_views(gs, cams)
+    assert len(rgbs) == 2 and rgbs[0].shape == (40, 48, 3) and alphas[0].shape == (40, 48, 1)
+    inp = H.view_inputs(gs, cams, 1)
+    colors = H.colors_from(R, inp, 2)
+    xys, depths, radii, conics, comp, tiles, cov3d = R.project_gaussians(
+        inp["means"], inp["scales"], 1, inp["quats"], inp["viewmat"], k["fx"], k["fy"], k["cx"], k["cy"], k["H"],
+        k["W"], 16)
+    img, alpha = R.rasterize_gaussians(xys, depths, radii, conics, tiles, colors, inp["opacities"], k["H"], k["W"],
+                                       16, background=inp["background"], return_alpha=True)
+    assert torch.allclose(rgbs[1], img.clamp(max=1.0), atol=1e-6)
+    assert torch.allclose(alphas[1][..., 0], alpha, atol=1e-6)
+    assert float(rgbs[1].max()) <= 1.0

@@ -90,8 +90,11 @@ SB_API int sb_cumsum_i32(int count, const int* in, int* out, void* temp, size_t 
                   sb_stream_t stream);
 
 /* ---- a6: gsplat.utils.map_gaussian_to_intersects (_C.map_gaussian_to_intersects) -------
- * key = ((view*T + tile) << 32) | float32 bits of depth; gaussian_ids are view-local. */
-SB_API int sb_map_gaussian_to_intersects(int num_views, int n, const float* xys, const float* depths,
+ * key = ((view*T + tile) << 32) | float32 bits of depth; gaussian_ids are view-local.
+ * xys_stride: floats between consecutive pixel centres (2 for a dense (V*N,2) array, 12 to read
+ * them straight out of the packed raster record); must be even (8-byte aligned float2 loads). */
+SB_API int sb_map_gaussian_to_intersects(int num_views, int n, const float* xys, int xys_stride,
+                                  const float* depths,
                                   const int* radii, const int* cum_tiles_hit, int tiles_x,
                                   int tiles_y, int block_width, int64_t* isect_ids,
                                   int* gaussian_ids, sb_stream_t stream);
@@ -111,27 +114,36 @@ SB_API int sb_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted
 /* ---- a10 / a11: gsplat.rasterize_gaussians (gs_utils.py:96-109) -------------------------
  * upstream bindings: _C.rasterize_forward / _C.rasterize_backward (3 channels).
  * The kernels read one packed 48-byte record per (view, Gaussian):
- *   [x, y, hx, hy | conic a, b, c, opacity | r, g, b, 0]   (hx, hy: conservative half
- *   extents of the region where alpha >= 1/255, used only to skip work)
- * built from the API tensors by sb_pack_splats.  Gradients come back in a packed
- * 48-byte record [v_x, v_y, v_ca, v_cb | v_cc, v_opacity, v_r, v_g | v_b, 0, 0, 0] that
- * the caller zero-fills; sb_unpack_splat_grads splits it into API tensors.
+ *   [x, y, hx, hy | A, B, C, log2(opacity) | r, g, b, opacity]
+ *   hx, hy: conservative half extents of the region where alpha >= 1/255 (used only to skip
+ *   work); A = -0.5*log2(e)*conic.a, B = -log2(e)*conic.b, C = -0.5*log2(e)*conic.c, so that
+ *   log2(alpha) = dx*(A*dx + B*dy) + C*dy*dy + log2(opacity).  Built from the API tensors by
+ *   sb_pack_splats.  Gradients come back in a packed 48-byte record of MOMENTS that the caller
+ *   zero-fills: [M1x, M1y, M2xx, M2xy | M2yy, M0, v_r, v_g | v_b, 0, 0, 0] with w = dL/dsigma per
+ *   (pixel, Gaussian) pair, M0 = sum w, M1x = sum w*dx, ... M2yy = sum w*dy*dy.
+ *   sb_unpack_splat_grads turns them into the API gradients: v_xy = (a*M1x + b*M1y,
+ *   b*M1x + c*M1y), v_conic = (M2xx/2, M2xy, M2yy/2), v_opacity = -M0/opacity.
  * cum_tiles_hit (V*N inclusive scan, may be NULL): when given, a view without a single
  * intersection gets out_img = background and final_T = 0 (alpha 1) -- the behaviour of
- * upstream's `num_intersects < 1` early return, applied per view on the device. */
+ * upstream's `num_intersects < 1` early return, applied per view on the device.
+ * out_alpha (may be NULL) receives 1 - final_T.  clamp_rgb_max1 != 0 stores min(rgb, 1) -- the
+ * wrapper's final clamp (gs_utils.py:111) folded into the kernel; the backward then takes that
+ * stored image as out_img_clamped (NULL otherwise) and passes no gradient through channels
+ * that reached 1. */
 SB_API int sb_pack_splats(int count, const float* xys, const float* conics, const float* colors,
                    const float* opacity, float* packed, sb_stream_t stream);
 SB_API int sb_rasterize_fwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
                      const int* tile_bins, const float* background, int img_h, int img_w,
                      int block_width, const int* cum_tiles_hit, float* out_img, float* final_ts,
-                     int* final_idx, sb_stream_t stream);
+                     int* final_idx, float* out_alpha, int clamp_rgb_max1, sb_stream_t stream);
 SB_API int sb_rasterize_bwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
                      const int* tile_bins, const float* background, int img_h, int img_w,
                      int block_width, const float* final_ts, const int* final_idx,
-                     const float* v_out_img, const float* v_out_alpha, float* v_packed,
-                     sb_stream_t stream);
-SB_API int sb_unpack_splat_grads(int count, const float* v_packed, float* v_xys, float* v_conics,
-                          float* v_colors, float* v_opacity, sb_stream_t stream);
+                     const float* v_out_img, const float* v_out_alpha,
+                     const float* out_img_clamped, float* v_packed, sb_stream_t stream);
+SB_API int sb_unpack_splat_grads(int count, const float* v_packed, const float* conics,
+                          const float* opacity, float* v_xys, float* v_conics, float* v_colors,
+                          float* v_opacity, sb_stream_t stream);
 
 /* ---- a1 / a2: fused multi-view projection + SH colour ----------------------------------
  * The view loop of rasterize_gaussians_to_multiimgs (gs_utils.py:20-27) with the per-view

@@ -28,14 +28,14 @@ SIGNATURES = {
     "sb_project_bwd": (I, [I, I, P, P, F, P, P, I, P, F, F, F, F, I, I, I, F, P, P, P, P, P, P, P, P, P, P, P]),
     "sb_cumsum_temp_bytes": (S, [I]),
     "sb_cumsum_i32": (I, [I, P, P, P, S, P]),
-    "sb_map_gaussian_to_intersects": (I, [I, I, P, P, P, P, I, I, I, P, P, P]),
+    "sb_map_gaussian_to_intersects": (I, [I, I, P, I, P, P, P, I, I, I, P, P, P]),
     "sb_sort_temp_bytes": (S, [I]),
     "sb_sort_pairs": (I, [I, I, P, P, P, P, P, S, P]),
     "sb_tile_bin_edges": (I, [I, P, I, P, P]),
     "sb_pack_splats": (I, [I, P, P, P, P, P, P]),
-    "sb_rasterize_fwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P]),
-    "sb_rasterize_bwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, P]),
-    "sb_unpack_splat_grads": (I, [I, P, P, P, P, P, P]),
+    "sb_rasterize_fwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, I, P]),
+    "sb_rasterize_bwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, P, P]),
+    "sb_unpack_splat_grads": (I, [I, P, P, P, P, P, P, P, P]),
     "sb_views_project_fwd": (I, [I, I, P, P, F, P, P, P, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P, P]),
     "sb_views_project_bwd": (I, [I, I, P, P, F, P, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P, P, P, P, P]),
 }

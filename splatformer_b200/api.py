@@ -186,17 +186,19 @@ class _RasterizeGaussians(Function):
         out_img = torch.empty(img_height, img_width, 3, dtype=F32, device=dev)
         final_ts = torch.empty(img_height, img_width, dtype=F32, device=dev)
         final_idx = torch.empty(img_height, img_width, dtype=I32, device=dev)
+        out_alpha = torch.empty(img_height, img_width, dtype=F32, device=dev) if return_alpha else None
         _abi.check(lib.sb_rasterize_fwd(
             1, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
             _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
             img_width, block_width, None, _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
-            _abi.ptr(final_idx, I32, "final_idx"), _abi.stream()), "sb_rasterize_fwd")
+            _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"), 0, _abi.stream()),
+            "sb_rasterize_fwd")
         ctx.empty = False
         ctx.num_intersects = num_intersects
         ctx.meta = (n, img_height, img_width, block_width)
-        ctx.save_for_backward(packed, gaussian_ids_sorted, tile_bins, background, final_ts, final_idx)
+        ctx.save_for_backward(packed, gaussian_ids_sorted, tile_bins, background, final_ts, final_idx, conics,
+                              opacity)
         ctx.set_materialize_grads(False)
-        out_alpha = 1 - final_ts
         return (out_img, out_alpha) if return_alpha else out_img
 
     @staticmethod
@@ -205,7 +207,8 @@ class _RasterizeGaussians(Function):
         if ctx.empty or (v_out_img is None and v_out_alpha is None):
             return none12
         lib = _abi.load()
-        packed, gaussian_ids_sorted, tile_bins, background, final_ts, final_idx = ctx.saved_tensors
+        (packed, gaussian_ids_sorted, tile_bins, background, final_ts, final_idx, conics,
+         opacity) = ctx.saved_tensors
         n, img_height, img_width, block_width = ctx.meta
         dev = packed.device
         v_out_img = torch.zeros(img_height, img_width, 3, dtype=F32, device=dev) if v_out_img is None \
@@ -216,14 +219,15 @@ class _RasterizeGaussians(Function):
             1, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
             _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
             img_width, block_width, _abi.ptr(final_ts, F32, "final_Ts"), _abi.ptr(final_idx, I32, "final_idx"),
-            _abi.ptr(v_out_img, F32, "v_out_img"), _abi.ptr(v_out_alpha, F32, "v_out_alpha"),
+            _abi.ptr(v_out_img, F32, "v_out_img"), _abi.ptr(v_out_alpha, F32, "v_out_alpha"), None,
             _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_bwd")
         v_xys = torch.empty(n, 2, dtype=F32, device=dev)
         v_conics = torch.empty(n, 3, dtype=F32, device=dev)
         v_colors = torch.empty(n, 3, dtype=F32, device=dev)
         v_opacity = torch.empty(n, 1, dtype=F32, device=dev)
         _abi.check(lib.sb_unpack_splat_grads(
-            n, _abi.ptr(v_packed, F32, "v_packed"), _abi.ptr(v_xys, F32, "v_xys"),
+            n, _abi.ptr(v_packed, F32, "v_packed"), _abi.ptr(conics, F32, "conics"),
+            _abi.ptr(opacity, F32, "opacity"), _abi.ptr(v_xys, F32, "v_xys"),
             _abi.ptr(v_conics, F32, "v_conics"), _abi.ptr(v_colors, F32, "v_colors"),
             _abi.ptr(v_opacity, F32, "v_opacity"), _abi.stream()), "sb_unpack_splat_grads")
         return (v_xys, None, None, v_conics, None, v_colors, v_opacity, None, None, None, None, None)

@@ -1,5 +1,5 @@
 // ABI bookkeeping + the small layout kernels around the rasteriser.
-#include "sb_common.cuh"
+#include "raster_common.cuh"
 
 namespace sb {
 
@@ -13,14 +13,15 @@ __global__ void __launch_bounds__(256) pack_kernel(int count, const float* __res
   const float2 c = __ldg(reinterpret_cast<const float2*>(xys) + i);
   const float ka = __ldg(conics + 3 * i), kb = __ldg(conics + 3 * i + 1), kc = __ldg(conics + 3 * i + 2);
   const float op = __ldg(opacity + i);
-  float hx, hy;
-  visible_extent(ka, kb, kc, op, hx, hy);
-  packed[3 * i] = make_float4(c.x, c.y, hx, hy);
-  packed[3 * i + 1] = make_float4(ka, kb, kc, op);
-  packed[3 * i + 2] = make_float4(__ldg(colors + 3 * i), __ldg(colors + 3 * i + 1), __ldg(colors + 3 * i + 2), 0.f);
+  float4 r0, r1, r2;
+  pack_record(c.x, c.y, ka, kb, kc, op, __ldg(colors + 3 * i), __ldg(colors + 3 * i + 1), __ldg(colors + 3 * i + 2),
+              r0, r1, r2);
+  packed[3 * i] = r0; packed[3 * i + 1] = r1; packed[3 * i + 2] = r2;
 }
 
 __global__ void __launch_bounds__(256) unpack_grads_kernel(int count, const float4* __restrict__ vp,
+                                                           const float* __restrict__ conics,
+                                                           const float* __restrict__ opacity,
                                                            float* __restrict__ v_xys,
                                                            float* __restrict__ v_conics,
                                                            float* __restrict__ v_colors,
@@ -28,9 +29,12 @@ __global__ void __launch_bounds__(256) unpack_grads_kernel(int count, const floa
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= count) return;
   const float4 a = __ldg(vp + 3 * i), b = __ldg(vp + 3 * i + 1), c = __ldg(vp + 3 * i + 2);
-  reinterpret_cast<float2*>(v_xys)[i] = make_float2(a.x, a.y);
-  v_conics[3 * i] = a.z; v_conics[3 * i + 1] = a.w; v_conics[3 * i + 2] = b.x;
-  v_opacity[i] = b.y;
+  float vx, vy, vca, vcb, vcc, vop;
+  moments_to_grads(a, b, __ldg(conics + 3 * i), __ldg(conics + 3 * i + 1), __ldg(conics + 3 * i + 2),
+                   __ldg(opacity + i), vx, vy, vca, vcb, vcc, vop);
+  reinterpret_cast<float2*>(v_xys)[i] = make_float2(vx, vy);
+  v_conics[3 * i] = vca; v_conics[3 * i + 1] = vcb; v_conics[3 * i + 2] = vcc;
+  v_opacity[i] = vop;
   v_colors[3 * i] = b.z; v_colors[3 * i + 1] = b.w; v_colors[3 * i + 2] = c.x;
 }
 
@@ -53,11 +57,12 @@ extern "C" int sb_pack_splats(int count, const float* xys, const float* conics, 
   SB_RETURN_LAST();
 }
 
-extern "C" int sb_unpack_splat_grads(int count, const float* v_packed, float* v_xys, float* v_conics,
+extern "C" int sb_unpack_splat_grads(int count, const float* v_packed, const float* conics,
+                                     const float* opacity, float* v_xys, float* v_conics,
                                      float* v_colors, float* v_opacity, sb_stream_t stream) {
   if (count < 0) return SB_ERR_BAD_ARG;
   if (count == 0) return 0;
   sb::unpack_grads_kernel<<<sb::ceil_div(count, 256), 256, 0, (cudaStream_t)stream>>>(
-      count, reinterpret_cast<const float4*>(v_packed), v_xys, v_conics, v_colors, v_opacity);
+      count, reinterpret_cast<const float4*>(v_packed), conics, opacity, v_xys, v_conics, v_colors, v_opacity);
   SB_RETURN_LAST();
 }

@@ -3,6 +3,7 @@
 // the views, recomputes the forward record (cheaper than storing ~50 floats per view) and sums
 // the per-view VJPs in registers, so v_means / v_scales / v_quats are written once.
 #include "sh_stage.cuh"
+#include "raster_common.cuh"
 
 namespace sb {
 
@@ -130,15 +131,19 @@ __global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
       const size_t i = (size_t)v * n + g;
       const float4 ga = __ldg(v_packed + 3 * i), gb = __ldg(v_packed + 3 * i + 1), gc = __ldg(v_packed + 3 * i + 2);
       float vm[3], vs[3], vq[4];
-      project_bwd_one(m, s, glob, cam, f, ga.x, ga.y, 0.f, ga.z, ga.w, gb.x, 0.f, nullptr, vm, vs, vq, nullptr);
+      const float4 col = __ldg(packed + 3 * i + 2);       // r, g, b (after the clamp), opacity
+      const float op = col.w;
+      float vx, vy, vca, vcb, vcc, vop;
+      moments_to_grads(ga, gb, f.ca, f.cb, f.cc, op, vx, vy, vca, vcb, vcc, vop);
+      project_bwd_one(m, s, glob, cam, f, vx, vy, 0.f, vca, vcb, vcc, 0.f, nullptr, vm, vs, vq, nullptr);
 #pragma unroll
       for (int k = 0; k < 3; ++k) { am[k] += vm[k]; as[k] += vs[k]; }
 #pragma unroll
       for (int k = 0; k < 4; ++k) aq[k] += vq[k];
-      aop += gb.y;
+      aop += vop;
       float vr = gb.z, vg = gb.w, vb = gc.x;
       if (DEG >= 0) {
-        const float4 col = __ldg(packed + 3 * i + 2);      // clamp(x + 0.5, min 0): gradient passes where > 0
+        // clamp(x + 0.5, min 0): gradient passes where > 0
         vr = col.x > 0.f ? vr : 0.f; vg = col.y > 0.f ? vg : 0.f; vb = col.z > 0.f ? vb : 0.f;
         float Y[KU];
         sh_basis(DEG, m[0] - __ldg(campos + 3 * v), m[1] - __ldg(campos + 3 * v + 1), m[2] - __ldg(campos + 3 * v + 2), Y);

@@ -5,6 +5,7 @@
 // separately, so that radii, tile counts, depth keys and pixel centres are bit-identical to the
 // oracle.  The kernel is a pure stream (100 B per Gaussian per view), so losing FMA costs nothing.
 #include "sh_stage.cuh"
+#include "raster_common.cuh"
 
 namespace sb {
 
@@ -100,12 +101,8 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     } else {
       r = c[0]; gg = c[1]; b = c[2];
     }
-    float hx, hy;
-    visible_extent(o.ca, o.cb, o.cc, op, hx, hy);
     float4* p = packed + 3 * i;
-    p[0] = make_float4(o.px, o.py, hx, hy);
-    p[1] = make_float4(o.ca, o.cb, o.cc, op);
-    p[2] = make_float4(r, gg, b, 0.f);
+    pack_record(o.px, o.py, o.ca, o.cb, o.cc, op, r, gg, b, p[0], p[1], p[2]);
   }
 }
 

@@ -2,10 +2,12 @@
 // _C.rasterize_forward behind gsplat.rasterize_gaussians, /root/reference/utils/gs_utils.py:96-109).
 //
 // One CTA per (tile, view).  The tile's depth-sorted Gaussians are staged through shared memory
-// in batches of 256 packed 48-byte records.  Each warp owns an 8x4 pixel rectangle: its lanes
-// first test 32 staged Gaussians against the rectangle in parallel (one ballot), then the warp
-// walks only the hits in depth order.  The skip is conservative (sb::visible_extent), so the
-// composited result is the one the plain per-pixel loop produces.
+// in batches of 256 packed 48-byte records (raster_common.cuh).  Each warp owns an 8x4 pixel
+// rectangle: its lanes first test 32 staged Gaussians against the rectangle in parallel (one
+// ballot), then the warp walks only the hits in depth order.  The skip is conservative
+// (sb::visible_extent), so the composited result is the one the plain per-pixel loop produces.
+// The walk is branch-free per lane (predicated selects), the kernel being issue-bound: per
+// (warp, hit) it costs 3 LDS + ~25 FP32/ALU operations + one MUFU.EX2.
 #include "raster_common.cuh"
 
 namespace sb {
@@ -14,7 +16,8 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ ids_sorted,
     const int2* __restrict__ tile_bins, const float* __restrict__ background, int tiles_x,
     int tiles_y, int img_w, int img_h, int bw, const int* __restrict__ cum_tiles_hit,
-    float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx) {
+    float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx,
+    float* __restrict__ out_alpha, int clamp_rgb) {
   __shared__ float4 sA[kBatch], sB[kBatch], sC[kBatch];
   const int tile = blockIdx.x, v = blockIdx.y;
   const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
@@ -39,6 +42,7 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
     }
     __syncthreads();
     if (__all_sync(0xffffffffu, done)) continue;
+    const int idx0 = range.x + b0;
     for (int c0 = 0; c0 < bsize; c0 += 32) {
       const int j = c0 + lane;
       bool hit = false;
@@ -47,20 +51,19 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
       while (mask) {
         const int k = c0 + __ffs(mask) - 1;
         mask &= mask - 1;
-        if (done) continue;
-        const float4 A = sA[k], B = sB[k];
+        const float4 A = sA[k], B = sB[k], C = sC[k];
         const float dx = A.x - px, dy = A.y - py;
-        const float sigma = 0.5f * (B.x * dx * dx + B.z * dy * dy) + B.y * dx * dy;
-        if (sigma < 0.f) continue;
-        const float alpha = fminf(kAlphaMax, B.w * __expf(-sigma));
-        if (alpha < kAlphaMin) continue;
+        const float pw = dx * fmaf(B.y, dy, B.x * dx) + B.z * dy * dy;      // -sigma * log2(e)
+        const float alpha = fminf(kAlphaMax, ex2_approx(pw + B.w));
+        const bool valid = !done && (pw <= 0.f) && (alpha >= kAlphaMin);
         const float next_T = T * (1.0f - alpha);
-        if (next_T <= kTMin) { done = true; continue; }
-        const float4 C = sC[k];
-        const float wgt = alpha * T;
-        pr += C.x * wgt; pg += C.y * wgt; pb += C.z * wgt;
-        T = next_T;
-        cur_idx = range.x + b0 + k;
+        const bool stop = valid && (next_T <= kTMin);
+        const bool upd = valid && !stop;
+        done = done || stop;
+        const float wgt = upd ? alpha * T : 0.f;
+        pr = fmaf(C.x, wgt, pr); pg = fmaf(C.y, wgt, pg); pb = fmaf(C.z, wgt, pb);
+        T = upd ? next_T : T;
+        cur_idx = upd ? idx0 + k : cur_idx;
       }
       if (__all_sync(0xffffffffu, done)) break;
     }
@@ -74,6 +77,7 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
       const int lo = v ? __ldg(cum_tiles_hit + (size_t)v * n - 1) : 0;
       if (hi - lo < 1) {
         final_ts[pix] = 0.f; final_idx[pix] = 0;
+        if (out_alpha) out_alpha[pix] = 1.f;
         out_img[3 * pix] = __ldg(background); out_img[3 * pix + 1] = __ldg(background + 1);
         out_img[3 * pix + 2] = __ldg(background + 2);
         return;
@@ -81,9 +85,10 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
     }
     final_ts[pix] = T;
     final_idx[pix] = cur_idx;
-    out_img[3 * pix] = pr + T * __ldg(background);
-    out_img[3 * pix + 1] = pg + T * __ldg(background + 1);
-    out_img[3 * pix + 2] = pb + T * __ldg(background + 2);
+    if (out_alpha) out_alpha[pix] = 1.0f - T;
+    float r = pr + T * __ldg(background), g = pg + T * __ldg(background + 1), b = pb + T * __ldg(background + 2);
+    if (clamp_rgb) { r = fminf(r, 1.0f); g = fminf(g, 1.0f); b = fminf(b, 1.0f); }   // gs_utils.py:111
+    out_img[3 * pix] = r; out_img[3 * pix + 1] = g; out_img[3 * pix + 2] = b;
   }
 }
 
@@ -93,7 +98,8 @@ extern "C" int sb_rasterize_fwd(int num_views, int n, const float* packed,
                                 const int* gaussian_ids_sorted, const int* tile_bins,
                                 const float* background, int img_h, int img_w, int block_width,
                                 const int* cum_tiles_hit, float* out_img, float* final_ts,
-                                int* final_idx, sb_stream_t stream) {
+                                int* final_idx, float* out_alpha, int clamp_rgb_max1,
+                                sb_stream_t stream) {
   if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || block_width < 2 || block_width > 16)
     return SB_ERR_BAD_ARG;
   const int tiles_x = sb::ceil_div(img_w, block_width), tiles_y = sb::ceil_div(img_h, block_width);
@@ -101,6 +107,6 @@ extern "C" int sb_rasterize_fwd(int num_views, int n, const float* packed,
   sb::raster_fwd_kernel<<<grid, sb::kRasterBlock, 0, (cudaStream_t)stream>>>(
       n, reinterpret_cast<const float4*>(packed), gaussian_ids_sorted,
       reinterpret_cast<const int2*>(tile_bins), background, tiles_x, tiles_y, img_w, img_h, block_width,
-      cum_tiles_hit, out_img, final_ts, final_idx);
+      cum_tiles_hit, out_img, final_ts, final_idx, out_alpha, clamp_rgb_max1);
   SB_RETURN_LAST();
 }

@@ -9,7 +9,7 @@
 namespace sb {
 
 __global__ void __launch_bounds__(256) map_isect_kernel(
-    int num_views, int n, const float* __restrict__ xys, const float* __restrict__ depths,
+    int num_views, int n, const float* __restrict__ xys, int xy_stride, const float* __restrict__ depths,
     const int* __restrict__ radii, const int* __restrict__ cum, int tiles_x, int tiles_y, int bw,
     int64_t* __restrict__ keys, int* __restrict__ gids) {
   const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
@@ -18,7 +18,7 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
   if (r <= 0) return;
   const int v = (int)(i / n);
   const int g = (int)(i - (size_t)v * n);
-  const float2 c = __ldg(reinterpret_cast<const float2*>(xys) + i);
+  const float2 c = __ldg(reinterpret_cast<const float2*>(xys + i * xy_stride));
   int min_x, max_x, min_y, max_y;
   tile_bbox(c.x, c.y, (float)r, tiles_x, tiles_y, bw, min_x, max_x, min_y, max_y);
   size_t k = i == 0 ? 0 : (size_t)__ldg(cum + i - 1);
@@ -62,16 +62,18 @@ extern "C" int sb_cumsum_i32(int count, const int* in, int* out, void* temp, siz
   return (int)cub::DeviceScan::InclusiveSum(temp, temp_bytes, in, out, count, (cudaStream_t)stream);
 }
 
-extern "C" int sb_map_gaussian_to_intersects(int num_views, int n, const float* xys,
+extern "C" int sb_map_gaussian_to_intersects(int num_views, int n, const float* xys, int xys_stride,
                                              const float* depths, const int* radii,
                                              const int* cum_tiles_hit, int tiles_x, int tiles_y,
                                              int block_width, int64_t* isect_ids, int* gaussian_ids,
                                              sb_stream_t stream) {
-  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16) return SB_ERR_BAD_ARG;
+  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || xys_stride < 2 || (xys_stride & 1))
+    return SB_ERR_BAD_ARG;
   const size_t total = (size_t)num_views * n;
   if (total == 0) return 0;
   sb::map_isect_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      num_views, n, xys, depths, radii, cum_tiles_hit, tiles_x, tiles_y, block_width, isect_ids, gaussian_ids);
+      num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit, tiles_x, tiles_y, block_width, isect_ids,
+      gaussian_ids);
   SB_RETURN_LAST();
 }
 

@@ -79,8 +79,8 @@ def render_scene(gs_params: Dict[str, Tensor], camera_to_worlds: Tensor, cx, cy,
                             dtype=torch.float32).to(means.device, non_blocking=True)
     intrins = intr.reshape(1, 4).expand(v, 4).contiguous()
     rgb, alpha = render_views(means, scales, quats, opacities, color_src, sh_degree, viewmats, campos, intrins,
-                              h, w, BLOCK_WIDTH, background=background_color.to(means.device))
-    return torch.clamp(rgb, max=1.0), alpha.unsqueeze(-1)
+                              h, w, BLOCK_WIDTH, background=background_color.to(means.device), clamp_rgb=True)
+    return rgb, alpha.unsqueeze(-1)
 
 
 def rasterize_gaussians_to_multiimgs(gs_params: Dict[str, Tensor], cameras: Dict[str, Tensor]

@@ -83,7 +83,7 @@ def _c(t: Tensor) -> Tensor:
 class _RenderViews(Function):
     @staticmethod
     def forward(ctx, means, scales, quats, opacities, color_src, viewmats, campos, intrins, sh_degree,
-                img_height, img_width, block_width, background, clip_thresh):
+                img_height, img_width, block_width, background, clip_thresh, clamp_rgb):
         lib = _abi.load()
         dev = means.device
         n = means.shape[0]
@@ -120,6 +120,7 @@ class _RenderViews(Function):
         out_img = torch.empty(v, img_height, img_width, 3, dtype=F32, device=dev)
         final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
         final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)
+        out_alpha = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
         with _stage("map_isect"):
             isect_ids, gaussian_ids = _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x,
                                            tiles_y, block_width)
@@ -133,24 +134,25 @@ class _RenderViews(Function):
                 _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
                 img_width, block_width, _abi.ptr(cum, I32, "cum_tiles_hit"), _abi.ptr(out_img, F32, "out_img"),
                 _abi.ptr(final_ts, F32, "final_Ts"),
-                _abi.ptr(final_idx, I32, "final_idx"), _abi.stream()), "sb_rasterize_fwd")
+                _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
+                1 if clamp_rgb else 0, _abi.stream()), "sb_rasterize_fwd")
         ctx.meta = (v, n, sh_degree, img_height, img_width, block_width, clip_thresh, vm_stride,
-                    tuple(color_src.shape), num_intersects)
+                    tuple(color_src.shape), num_intersects, clamp_rgb)
         ctx.save_for_backward(means, scales, quats, viewmats, campos, intrins, background, packed,
-                              gids_sorted, tile_bins, final_ts, final_idx)
+                              gids_sorted, tile_bins, final_ts, final_idx, out_img if clamp_rgb else None)
         ctx.set_materialize_grads(False)
-        return out_img, 1 - final_ts
+        return out_img, out_alpha
 
     @staticmethod
     def backward(ctx, v_out_img, v_out_alpha):
         lib = _abi.load()
         (means, scales, quats, viewmats, campos, intrins, background, packed, gids_sorted, tile_bins,
-         final_ts, final_idx) = ctx.saved_tensors
+         final_ts, final_idx, out_img_clamped) = ctx.saved_tensors
         (v, n, sh_degree, img_height, img_width, block_width, clip_thresh, vm_stride, color_shape,
-         num_intersects) = ctx.meta
+         num_intersects, clamp_rgb) = ctx.meta
         dev = means.device
         if v_out_img is None and v_out_alpha is None:
-            return (None,) * 14
+            return (None,) * 15
         v_out_img = torch.zeros(v, img_height, img_width, 3, dtype=F32, device=dev) if v_out_img is None \
             else _c(v_out_img)
         v_out_alpha = None if v_out_alpha is None else _c(v_out_alpha)
@@ -162,8 +164,8 @@ class _RenderViews(Function):
                 _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
                 img_width, block_width, _abi.ptr(final_ts, F32, "final_Ts"),
                 _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(v_out_img, F32, "v_out_img"),
-                _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(v_packed, F32, "v_packed"),
-                _abi.stream()), "sb_rasterize_bwd")
+                _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(out_img_clamped, F32, "out_img"),
+                _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_bwd")
         v_means = torch.empty(n, 3, dtype=F32, device=dev)
         v_scales = torch.empty(n, 3, dtype=F32, device=dev)
         v_quats = torch.empty(n, 4, dtype=F32, device=dev)
@@ -180,29 +182,29 @@ class _RenderViews(Function):
                 _abi.ptr(v_opac, F32, "v_opacities"), _abi.ptr(v_color, F32, "v_color_src"), _abi.stream()),
                 "sb_views_project_bwd")
         return (v_means, v_scales, v_quats, v_opac, v_color, None, None, None, None, None, None, None, None,
-                None)
+                None, None)
 
 
 def _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x, tiles_y, block_width):
-    """Key emission for the batched path reads pixel centres straight from the packed record
-    (stride 12 floats) -- the ABI's map function takes contiguous (V*N, 2) xys, so gather them."""
-    xys = packed.view(v * n, 12)[:, :2].contiguous()
-    return utils.map_gaussian_to_intersects(n, num_intersects, xys, depths.view(-1), radii.view(-1), cum,
-                                            (tiles_x, tiles_y, 1), block_width, num_views=v)
+    """Key emission for the batched path reads the pixel centres straight out of the packed record
+    (stride 12 floats)."""
+    return utils.map_gaussian_to_intersects(n, num_intersects, packed, depths.view(-1), radii.view(-1), cum,
+                                            (tiles_x, tiles_y, 1), block_width, num_views=v, xys_stride=12)
 
 
 def render_views(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor, color_src: Tensor,
                  sh_degree: int, viewmats: Tensor, campos: Optional[Tensor], intrins: Tensor,
                  img_height: int, img_width: int, block_width: int = 16,
-                 background: Optional[Tensor] = None, clip_thresh: float = 0.01):
+                 background: Optional[Tensor] = None, clip_thresh: float = 0.01, clamp_rgb: bool = False):
     """Render all V views of one scene.
 
     means (N,3), scales (N,3, activated), quats (N,4, unit), opacities (N,1|N, activated);
     color_src: (N,K,3) SH coefficients with sh_degree in 0..4 (colour = max(SH + 0.5, 0) as
     gs_utils.py:78-79) or (N,3) rgb with sh_degree = -1; viewmats (V,3|4,4) world->camera;
     campos (V,3) camera centres; intrins (V,4) = fx, fy, cx, cy.
-    Returns rgb (V,H,W,3) (not clamped) and alpha (V,H,W).  Differentiable in means, scales, quats,
-    opacities and color_src."""
+    Returns rgb (V,H,W,3) and alpha (V,H,W).  rgb is not clamped unless clamp_rgb=True, which folds
+    the wrapper's torch.clamp(rgb, max=1) (gs_utils.py:111) into the kernels.  Differentiable in
+    means, scales, quats, opacities and color_src."""
     assert 2 <= block_width <= 16, "block_width must be between 2 and 16"
     if not means.is_cuda:
         raise RuntimeError("render_views needs CUDA tensors (there is no CPU path)")
@@ -212,4 +214,4 @@ def render_views(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor
         campos = torch.zeros(viewmats.shape[0], 3, dtype=F32, device=means.device)
     return _RenderViews.apply(means, scales, quats, opacities, color_src, viewmats, campos, intrins,
                               int(sh_degree), int(img_height), int(img_width), int(block_width), background,
-                              float(clip_thresh))
+                              float(clip_thresh), bool(clamp_rgb))

@@ -34,13 +34,15 @@ def compute_cumulative_intersects(num_tiles_hit: Tensor) -> Tuple[int, Tensor]:
 
 def map_gaussian_to_intersects(num_points: int, num_intersects: int, xys: Tensor, depths: Tensor,
                                radii: Tensor, cum_tiles_hit: Tensor, tile_bounds, block_width: int,
-                               num_views: int = 1) -> Tuple[Tensor, Tensor]:
+                               num_views: int = 1, xys_stride: int = 2) -> Tuple[Tensor, Tensor]:
+    """`xys_stride` = 12 lets the fused path pass its packed raster record (whose first two floats are
+    the pixel centre) instead of a dense (V*N, 2) tensor."""
     lib = _abi.load()
     dev = xys.device
     isect_ids = torch.empty(num_intersects, dtype=torch.int64, device=dev)
     gaussian_ids = torch.empty(num_intersects, dtype=torch.int32, device=dev)
     _abi.check(lib.sb_map_gaussian_to_intersects(
-        num_views, num_points, _abi.ptr(xys.contiguous(), torch.float32, "xys"),
+        num_views, num_points, _abi.ptr(xys.contiguous(), torch.float32, "xys"), xys_stride,
         _abi.ptr(depths.contiguous(), torch.float32, "depths"),
         _abi.ptr(radii.contiguous(), torch.int32, "radii"),
         _abi.ptr(cum_tiles_hit.contiguous(), torch.int32, "cum_tiles_hit"),

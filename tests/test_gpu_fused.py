@@ -56,7 +56,7 @@ def test_fused_matches_per_view_api(cuda, sb_lib, n, deg, size, views):
     loss_a.backward()
     loss_b.backward()
     for name in gs:
-        H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name, rtol=1e-4)
+        H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name)   # summation order differs (atomics)
 
 
 def test_fused_matches_oracle_wrapper(cuda, sb_lib):

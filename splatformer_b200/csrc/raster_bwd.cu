@@ -2,38 +2,96 @@
 // gsplat.rasterize_gaussians' autograd, /root/reference/utils/gs_utils.py:96-109, train.py:289).
 //
 // Same CTA/warp decomposition as the forward kernel, walking each tile's list back to front.
-// Per pair the kernel produces w = dL/dsigma and three colour gradients; what leaves the warp are
-// nine sums per (warp, Gaussian): the moments {w, w dx, w dy, w dx^2, w dx dy, w dy^2} and the rgb
-// gradient (raster_common.cuh explains how the consumers turn moments into v_xy / v_conic /
-// v_opacity).  Eight of them are summed with a halving butterfly (4+2+1 exchange steps + 2 plain
-// steps = 9 shuffles for 8 values), the ninth with a plain 5-step butterfly, and nine lanes issue
-// one red.global.add.f32 each.
+// Per (pixel, Gaussian) pair the walk produces two numbers: w = dL/dsigma and fac = alpha * T (the
+// weight of the colour gradient).  What has to leave the warp are nine sums per (warp, Gaussian):
+// the moments {w, w dx, w dy, w dx^2, w dx dy, w dy^2} and fac * v_out[rgb] (raster_common.cuh
+// explains how the consumers turn moments into v_xy / v_conic / v_opacity).
+//
+// TRANSPOSED REDUCTION.  A butterfly reduction per hit costs ~55 issue slots for 9 values.  Instead
+// every lane parks its (w, fac) pair of a hit in a per-warp shared-memory slot; once 16 hits are
+// parked the warp transposes roles: lane j takes slot (j & 15) and sums that hit over the 16 pixels
+// of half (j >> 4) of the warp's 8x4 rectangle, with the pixel offsets as compile-time immediates
+// (raw moments about the rectangle corner, shifted to the Gaussian centre afterwards).  One
+// shuffle step joins the halves and the 16 owners issue two red.global.add.v4.f32 + one scalar red
+// each.  Cost: ~14 issue slots per hit.
 #include "raster_common.cuh"
 
 namespace sb {
 
-#define SB_XCHG(a, b, up, delta)                                        \
-  {                                                                     \
-    const float send_ = (up) ? (a) : (b);                               \
-    const float keep_ = (up) ? (b) : (a);                               \
-    (a) = keep_ + __shfl_xor_sync(0xffffffffu, send_, (delta));         \
-  }
+constexpr int kSlots = 16;          // hits parked per warp before a flush
+constexpr int kSlotStride = 33;     // float2 units; odd stride keeps the transposed LDS.64 conflict-free
+constexpr int kWarps = kRasterBlock / 32;
+constexpr size_t kBwdSmem = sizeof(float4) * (3 * kBatch + kWarps * 32) + sizeof(float2) * kWarps * kSlots * kSlotStride
+                            + sizeof(int) * kBatch;
 
-// On return lane L holds in v[0] the warp-wide sum of value (L >> 2) of v[0..7], and the return
-// value is the warp-wide sum of v8 (in every lane).
-__device__ __forceinline__ float warp_sum_8p1(float (&v)[8], float v8, int lane) {
-  const bool u16 = lane & 16, u8 = lane & 8, u4 = lane & 4;
-  SB_XCHG(v[0], v[4], u16, 16) SB_XCHG(v[1], v[5], u16, 16) SB_XCHG(v[2], v[6], u16, 16) SB_XCHG(v[3], v[7], u16, 16)
-  SB_XCHG(v[0], v[2], u8, 8) SB_XCHG(v[1], v[3], u8, 8)
-  SB_XCHG(v[0], v[1], u4, 4)
-  v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
-  v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, o);
-  return v8;
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
-#undef SB_XCHG
 
+// Sums the parked hits of this warp and issues the global reductions.
+//   RECT: the warp's pixels form the 8x4 rectangle with corner pixel centre (ox, oy), lane = 8*row + col
+//   otherwise the per-lane pixel centres are read from sP.
+template <bool RECT>
+__device__ __forceinline__ void flush_slots(const float2* __restrict__ myW, const float4* __restrict__ myVo,
+                                            const float2* __restrict__ myP, int nslot, int lane, float own_x,
+                                            float own_y, int own_g, float ox, float oy, float* __restrict__ vgrad) {
+  __syncwarp();
+  const int sj = lane & 15, h = lane >> 4;
+  const float2* row = myW + sj * kSlotStride + h * 16;
+  const float4* vo = myVo + h * 16;
+  float m0 = 0.f, m1x = 0.f, m1y = 0.f, m2xx = 0.f, m2xy = 0.f, m2yy = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+  if (RECT) {
+    float sx = 0.f, sy = 0.f, sxx = 0.f, sxy = 0.f, syy = 0.f;
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+      const float2 wf = row[t];
+      const float4 o = vo[t];
+      const float ix = (float)(t & 7), iy = (float)(t >> 3);
+      m0 += wf.x;
+      if (t & 7) { sx = fmaf(wf.x, ix, sx); sxx = fmaf(wf.x, ix * ix, sxx); }
+      if (t >> 3) { sy = fmaf(wf.x, iy, sy); syy = fmaf(wf.x, iy * iy, syy); }
+      if ((t & 7) && (t >> 3)) sxy = fmaf(wf.x, ix * iy, sxy);
+      cr = fmaf(wf.y, o.x, cr); cg = fmaf(wf.y, o.y, cg); cb = fmaf(wf.y, o.z, cb);
+    }
+    const float ax = own_x - ox, ay = own_y - (oy + (float)(2 * h));
+    m1x = ax * m0 - sx;
+    m1y = ay * m0 - sy;
+    m2xx = ax * (m1x - sx) + sxx;
+    m2xy = ay * m1x - ax * sy + sxy;
+    m2yy = ay * (m1y - sy) + syy;
+  } else {
+    const float2* pp = myP + h * 16;
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+      const float2 wf = row[t];
+      const float4 o = vo[t];
+      const float2 pc = pp[t];
+      const float dx = own_x - pc.x, dy = own_y - pc.y;
+      const float wdx = wf.x * dx, wdy = wf.x * dy;
+      m0 += wf.x; m1x += wdx; m1y += wdy;
+      m2xx = fmaf(wdx, dx, m2xx); m2xy = fmaf(wdx, dy, m2xy); m2yy = fmaf(wdy, dy, m2yy);
+      cr = fmaf(wf.y, o.x, cr); cg = fmaf(wf.y, o.y, cg); cb = fmaf(wf.y, o.z, cb);
+    }
+  }
+  m0 += __shfl_xor_sync(0xffffffffu, m0, 16);
+  m1x += __shfl_xor_sync(0xffffffffu, m1x, 16);
+  m1y += __shfl_xor_sync(0xffffffffu, m1y, 16);
+  m2xx += __shfl_xor_sync(0xffffffffu, m2xx, 16);
+  m2xy += __shfl_xor_sync(0xffffffffu, m2xy, 16);
+  m2yy += __shfl_xor_sync(0xffffffffu, m2yy, 16);
+  cr += __shfl_xor_sync(0xffffffffu, cr, 16);
+  cg += __shfl_xor_sync(0xffffffffu, cg, 16);
+  cb += __shfl_xor_sync(0xffffffffu, cb, 16);
+  if (h == 0 && sj < nslot) {
+    float* dst = vgrad + (size_t)own_g * 12;
+    red_add_v4(dst, m1x, m1y, m2xx, m2xy);
+    red_add_v4(dst + 4, m2yy, m0, cr, cg);
+    if (cb != 0.f) atomicAdd(dst + 8, cb);
+  }
+  __syncwarp();
+}
+
+template <bool RECT>
 __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ ids_sorted,
     const int2* __restrict__ tile_bins, const float* __restrict__ background, int tiles_x,
@@ -41,13 +99,18 @@ __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
     const int* __restrict__ final_idx, const float* __restrict__ v_out_img,
     const float* __restrict__ v_out_alpha, const float* __restrict__ out_img_clamped,
     float* __restrict__ v_packed) {
-  __shared__ float4 sA[kBatch], sB[kBatch], sC[kBatch];
-  __shared__ int sG[kBatch];
+  extern __shared__ float4 smem4[];
+  float4* sA = smem4;
+  float4* sB = sA + kBatch;
+  float4* sC = sB + kBatch;
+  float4* sVo = sC + kBatch;                                       // [kWarps][32]  v_out rgb per pixel
+  float2* sW = reinterpret_cast<float2*>(sVo + kWarps * 32);       // [kWarps][kSlots][kSlotStride]
+  int* sG = reinterpret_cast<int*>(sW + kWarps * kSlots * kSlotStride);
   const int tile = blockIdx.x, v = blockIdx.y;
   const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
   const PixelMap pm = make_pixel_map(tile_x, tile_y, bw, img_w, img_h);
   const float px = (float)pm.px_i + 0.5f, py = (float)pm.py_i + 0.5f;
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int2 range = __ldg(tile_bins + (size_t)v * tiles_x * tiles_y + tile);
   const int count = range.y - range.x;
   if (count <= 0) return;
@@ -69,18 +132,24 @@ __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
       if (!(__ldg(out_img_clamped + 3 * pix + 2) < 1.0f)) vo_b = 0.f;
     }
   }
+  float4* myVo = sVo + warp * 32;
+  float2* myW = sW + warp * kSlots * kSlotStride;
+  myVo[lane] = make_float4(vo_r, vo_g, vo_b, 0.f);
+  __shared__ float2 sP[RECT ? 1 : kWarps * 32];      // per-lane pixel centres (block widths other than 16)
+  const float2* myP = sP;
+  if (!RECT) { sP[warp * 32 + lane] = make_float2(px, py); myP = sP + warp * 32; }
+  const float ox = (float)(tile_x * bw + (warp & 1) * 8) + 0.5f;
+  const float oy = (float)(tile_y * bw + (warp >> 1) * 4) + 0.5f;
   const float bg_dot = __ldg(background) * vo_r + __ldg(background + 1) * vo_g + __ldg(background + 2) * vo_b;
   const int warp_final = __reduce_max_sync(0xffffffffu, bin_final);
   // v_alpha = T * (rgb . v_out) - ra * acc,  acc = sum_{behind} fac_j (rgb_j . v_out) - T_final (v_out_alpha - bg . v_out)
   float T = T_final;
   float acc = -T_final * (vo_a - bg_dot);
-  // lane -> which reduced value it owns, and whether it issues the global reduction
-  const int my_slot = (lane == 1) ? 8 : (lane >> 2);
-  const bool writer = ((lane & 3) == 0) || (lane == 1);
+  int nslot = 0;
+  float own_x = 0.f, own_y = 0.f;
+  int own_g = 0;
 
   for (int b0 = 0; b0 < count; b0 += kBatch) {
-    // everything at list positions above the warp's last composited Gaussian is untouched; once the
-    // whole CTA is past its positions nothing is left to do
     __syncthreads();
     const int bsize = min(kBatch, count - b0);
     if (threadIdx.x < bsize) {
@@ -91,6 +160,7 @@ __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
     }
     __syncthreads();
     for (int c0 = 0; c0 < bsize; c0 += 32) {
+      // everything at list positions above the warp's last composited Gaussian is untouched
       const int hi_idx = range.y - 1 - b0 - c0;       // list index of slot c0
       if (hi_idx - 31 > warp_final) continue;
       const int j = c0 + lane;
@@ -117,16 +187,16 @@ __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
         acc = fmaf(fac, cdot, acc);
         // d alpha / d sigma = -alpha_raw where the 0.999 clamp is inactive, 0 where it is active
         const float w = (valid && alpha_raw <= kAlphaMax) ? -alpha_raw * v_alpha : 0.f;
-        float vals[8];
-        const float wdx = w * dx, wdy = w * dy;
-        vals[0] = wdx; vals[1] = wdy; vals[2] = wdx * dx; vals[3] = wdx * dy;
-        vals[4] = wdy * dy; vals[5] = w; vals[6] = fac * vo_r; vals[7] = fac * vo_g;
-        const float s8 = warp_sum_8p1(vals, fac * vo_b, lane);
-        const float total = (lane == 1) ? s8 : vals[0];
-        if (writer && total != 0.f) atomicAdd(vgrad + (size_t)sG[k] * 12 + my_slot, total);
+        myW[nslot * kSlotStride + lane] = make_float2(w, fac);
+        if ((lane & 15) == nslot) { own_x = A.x; own_y = A.y; own_g = sG[k]; }
+        if (++nslot == kSlots) {
+          flush_slots<RECT>(myW, myVo, myP, kSlots, lane, own_x, own_y, own_g, ox, oy, vgrad);
+          nslot = 0;
+        }
       }
     }
   }
+  if (nslot) flush_slots<RECT>(myW, myVo, myP, nslot, lane, own_x, own_y, own_g, ox, oy, vgrad);
 }
 
 }  // namespace sb
@@ -141,9 +211,15 @@ extern "C" int sb_rasterize_bwd(int num_views, int n, const float* packed,
     return SB_ERR_BAD_ARG;
   const int tiles_x = sb::ceil_div(img_w, block_width), tiles_y = sb::ceil_div(img_h, block_width);
   dim3 grid(tiles_x * tiles_y, num_views);
-  sb::raster_bwd_kernel<<<grid, sb::kRasterBlock, 0, (cudaStream_t)stream>>>(
-      n, reinterpret_cast<const float4*>(packed), gaussian_ids_sorted,
-      reinterpret_cast<const int2*>(tile_bins), background, tiles_x, tiles_y, img_w, img_h, block_width,
-      final_ts, final_idx, v_out_img, v_out_alpha, out_img_clamped, v_packed);
+  // opting in to > 48 KB of dynamic shared memory is idempotent per-function state, not library state
+  cudaFuncSetAttribute(sb::raster_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb::kBwdSmem);
+  cudaFuncSetAttribute(sb::raster_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb::kBwdSmem);
+#define SB_LAUNCH(RECT)                                                                                   \
+  sb::raster_bwd_kernel<RECT><<<grid, sb::kRasterBlock, sb::kBwdSmem, (cudaStream_t)stream>>>(            \
+      n, reinterpret_cast<const float4*>(packed), gaussian_ids_sorted,                                    \
+      reinterpret_cast<const int2*>(tile_bins), background, tiles_x, tiles_y, img_w, img_h, block_width,  \
+      final_ts, final_idx, v_out_img, v_out_alpha, out_img_clamped, v_packed)
+  if (block_width == 16) SB_LAUNCH(true); else SB_LAUNCH(false);
+#undef SB_LAUNCH
   SB_RETURN_LAST();
 }

@@ -2,7 +2,8 @@
 // _C.rasterize_forward behind gsplat.rasterize_gaussians, /root/reference/utils/gs_utils.py:96-109).
 //
 // One CTA per (tile, view).  The tile's depth-sorted Gaussians are staged through shared memory
-// in batches of 256 packed 48-byte records (raster_common.cuh).  Each warp owns an 8x4 pixel
+// in batches of 256 packed 48-byte records (raster_common.cuh), double-buffered with cp.async so
+// that the gather of batch b+1 overlaps the compositing of batch b (one barrier per batch).  Each warp owns an 8x4 pixel
 // rectangle: its lanes first test 32 staged Gaussians against the rectangle in parallel (one
 // ballot), then the warp walks only the hits in depth order.  The skip is conservative
 // (sb::visible_extent), so the composited result is the one the plain per-pixel loop produces.
@@ -18,7 +19,7 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
     int tiles_y, int img_w, int img_h, int bw, const int* __restrict__ cum_tiles_hit,
     float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx,
     float* __restrict__ out_alpha, int clamp_rgb) {
-  __shared__ float4 sA[kBatch], sB[kBatch], sC[kBatch];
+  __shared__ float4 sAll[2][3][kBatch];          // double-buffered staging: [buffer][record word][slot]
   const int tile = blockIdx.x, v = blockIdx.y;
   const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
   const PixelMap pm = make_pixel_map(tile_x, tile_y, bw, img_w, img_h);
@@ -32,15 +33,35 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
   int cur_idx = 0;
   bool done = !pm.inside;
 
-  for (int b0 = 0; b0 < count; b0 += kBatch) {
-    if (__syncthreads_count(done) == kRasterBlock) break;
-    const int bsize = min(kBatch, count - b0);
-    if (threadIdx.x < bsize) {
-      const int g = __ldg(ids_sorted + range.x + b0 + threadIdx.x);
+  // software pipeline: ids are fetched two batches ahead (register), records one batch ahead (cp.async)
+  auto fetch_id = [&](int b0) -> int {
+    const int i = b0 + (int)threadIdx.x;
+    return i < count ? __ldg(ids_sorted + range.x + i) : -1;
+  };
+  auto stage = [&](int buf, int g) {
+    if (g >= 0) {
       const float4* p = vp + (size_t)g * 3;
-      sA[threadIdx.x] = __ldg(p); sB[threadIdx.x] = __ldg(p + 1); sC[threadIdx.x] = __ldg(p + 2);
+      cp_async16(&sAll[buf][0][threadIdx.x], p);
+      cp_async16(&sAll[buf][1][threadIdx.x], p + 1);
+      cp_async16(&sAll[buf][2][threadIdx.x], p + 2);
     }
-    __syncthreads();
+    cp_async_commit();
+  };
+  int g_next = fetch_id(0);
+  stage(0, g_next);
+  g_next = fetch_id(kBatch);
+
+  for (int b0 = 0, buf = 0; b0 < count; b0 += kBatch, buf ^= 1) {
+    cp_async_wait_all();
+    if (__syncthreads_count(done) == kRasterBlock) break;
+    if (b0 + kBatch < count) {
+      stage(buf ^ 1, g_next);
+      g_next = fetch_id(b0 + 2 * kBatch);
+    }
+    const int bsize = min(kBatch, count - b0);
+    const float4* sA = sAll[buf][0];
+    const float4* sB = sAll[buf][1];
+    const float4* sC = sAll[buf][2];
     if (__all_sync(0xffffffffu, done)) continue;
     const int idx0 = range.x + b0;
     for (int c0 = 0; c0 < bsize; c0 += 32) {
@@ -68,6 +89,7 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
       if (__all_sync(0xffffffffu, done)) break;
     }
   }
+  cp_async_wait_all();
   if (pm.inside) {
     const size_t pix = ((size_t)v * img_h + pm.py_i) * img_w + pm.px_i;
     if (cum_tiles_hit) {

@@ -5,8 +5,9 @@
 
 A *step* is one pass of the hot path over one scene: forward + backward of the render loss
 `mean(abs(rgb - gt))` (/root/reference/train.py:273-275,289) over all V views of a
-100k-Gaussian / SH3 / 512x512 scene (BASELINE.json configs[1]), through the drop-in wrapper
-`rasterize_gaussians_to_multiimgs` (/root/reference/utils/gs_utils.py:20).
+100k-Gaussian / SH3 / 512x512 scene (BASELINE.json configs[1]), through the public call
+`splatformer_b200.gs_utils.render_l1_loss` = `rasterize_gaussians_to_multiimgs`
+(/root/reference/utils/gs_utils.py:20) + the L1 loop of train.py:274-275 in one autograd node.
 
   value   whole-job Mpix/s with the scene, cameras and targets already resident in HBM
           (CUDA events, barrier + synchronize on both sides, max over ranks)
@@ -264,12 +265,13 @@ def main() -> None:
     for s in range(NSCENE):
         sid = (s if args.shard == "view" else rank * NSCENE + s)
         gs, cams, gt = synth.make_config(WORKLOAD, sid, num_views=V)
+        gt = (gt * 255.0).round().to(torch.uint8)        # 8-bit target images, as they are on disk
         cams = dict(cams)
         cams["camera_to_worlds"] = cams["camera_to_worlds"][view_lo:view_hi].contiguous()
         gt = gt[view_lo:view_hi].contiguous()
         scenes.append((gs, cams, gt))
     v_local = view_hi - view_lo
-    norm = 1.0 / (V * H * W * 3)            # mean over all V views of the scene, also when view-sharded
+    inv_views = 1.0 / V                     # mean over all V views of the scene, also when view-sharded
 
     host = [({k: v.pin_memory() for k, v in gs.items()}, {k: v.pin_memory() for k, v in cams.items()},
              gt.pin_memory()) for gs, cams, gt in scenes]
@@ -280,9 +282,9 @@ def main() -> None:
         + host[0][2].numel() * host[0][2].element_size()
 
     def render_loss(raw, cams, gt):
-        # render_scene is rasterize_gaussians_to_multiimgs without the final unbind into a Python list
-        rgb, _ = gs_utils.render_scene(raw, **cams)
-        return (rgb - gt).abs().sum() * norm
+        # train.py:272-275 in one public call: per-view mean |pred - gt| of all views of the scene
+        l1, _ = gs_utils.render_l1_loss(raw, cams, gt)
+        return l1.sum() * inv_views
 
     def sync_grads(raw):
         if args.shard == "view" and world > 1:
@@ -297,21 +299,13 @@ def main() -> None:
         sync_grads(raw)
         return loss
 
-    copy_stream = torch.cuda.Stream()
-
     def step_e2e(i):
         hgs, hcams, hgt = host[i % NSCENE]
-        main = torch.cuda.current_stream()
         raw = {k: v.to(dev, non_blocking=True).requires_grad_() for k, v in hgs.items()}
         cams = {k: v.to(dev, non_blocking=True) for k, v in hcams.items()}
-        # the targets are only needed by the loss: their copy overlaps the forward render
-        copy_stream.wait_stream(main)
-        with torch.cuda.stream(copy_stream):
-            gt = hgt.to(dev, non_blocking=True)
-        rgb, _ = gs_utils.render_scene(raw, **cams)
-        main.wait_stream(copy_stream)
-        gt.record_stream(main)
-        loss = (rgb - gt).abs().sum() * norm
+        # the pinned host targets go in as they are: render_l1_loss uploads them on a side stream
+        # underneath the projection / sort stages (they are first needed by the raster kernel)
+        loss = render_loss(raw, cams, hgt)
         loss.backward()
         sync_grads(raw)
         return float(loss.item())          # device->host read of the step's result
@@ -391,7 +385,7 @@ def main() -> None:
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak" if args.shard == "scene" else "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic",
+            "data": "synthetic (seeded shell scene, orbit cameras, uint8 random target images)",
             "config": {"workload": WORKLOAD, "gaussians": n, "sh_degree": deg, "views": V, "image": [H, W],
                        "scenes_per_step": scenes_per_step, "sharding": args.shard if world > 1 else "single",
                        "l2": f"inputs rotate over {NSCENE} scenes per rank ({NSCENE * h2d_bytes / 1e6:.0f} MB) and "
@@ -406,7 +400,7 @@ def main() -> None:
             e2e_step = e2e_ms / args.steps
             line["e2e"] = {"value": pix_step / (e2e_step * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_step,
                            "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4,
-                           "api": "splatformer_b200.gs_utils.render_scene (= rasterize_gaussians_to_multiimgs, stacked) + L1 loss + backward"}
+                           "api": "splatformer_b200.gs_utils.render_l1_loss(gs_params, cameras, images) + backward"}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args.cpu_views)
         print(json.dumps(line), flush=True)

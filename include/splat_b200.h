@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define SB_ABI_VERSION 1
+#define SB_ABI_VERSION 2
 #define SB_ERR_BAD_ARG (-1)
 #define SB_ERR_TEMP_TOO_SMALL (-2)
 
@@ -128,19 +128,27 @@ SB_API int sb_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted
  * upstream's `num_intersects < 1` early return, applied per view on the device.
  * out_alpha (may be NULL) receives 1 - final_T.  clamp_rgb_max1 != 0 stores min(rgb, 1) -- the
  * wrapper's final clamp (gs_utils.py:111) folded into the kernel; the backward then takes that
- * stored image as out_img_clamped (NULL otherwise) and passes no gradient through channels
- * that reached 1. */
+ * stored image as out_img with clamped_rgb_max1 != 0 and passes no gradient through channels
+ * that reached 1.
+ * Fused render loss (the step right after the path, train.py:275,278): with gt (V,H,W,3) given
+ * (float32 in [0,1], or uint8 with gt_is_u8 != 0, read as value / 255),
+ * the forward also writes loss_partial (V, T, 2) = per-tile sums of |rgb - gt| and (rgb - gt)^2
+ * (deterministic; the caller sums them), and the backward derives the image gradient itself:
+ * v_out = v_loss[view] * sign(out_img - gt) (+ v_out_img if that is given too), so neither the
+ * loss nor its gradient image ever exists as a tensor.  v_loss is a (V,) device array. */
 SB_API int sb_pack_splats(int count, const float* xys, const float* conics, const float* colors,
                    const float* opacity, float* packed, sb_stream_t stream);
 SB_API int sb_rasterize_fwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
                      const int* tile_bins, const float* background, int img_h, int img_w,
                      int block_width, const int* cum_tiles_hit, float* out_img, float* final_ts,
-                     int* final_idx, float* out_alpha, int clamp_rgb_max1, sb_stream_t stream);
+                     int* final_idx, float* out_alpha, int clamp_rgb_max1, const void* gt,
+                     int gt_is_u8, float* loss_partial, sb_stream_t stream);
 SB_API int sb_rasterize_bwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
                      const int* tile_bins, const float* background, int img_h, int img_w,
                      int block_width, const float* final_ts, const int* final_idx,
-                     const float* v_out_img, const float* v_out_alpha,
-                     const float* out_img_clamped, float* v_packed, sb_stream_t stream);
+                     const float* v_out_img, const float* v_out_alpha, const float* out_img,
+                     int clamped_rgb_max1, const void* gt, int gt_is_u8, const float* v_loss,
+                     float* v_packed, sb_stream_t stream);
 SB_API int sb_unpack_splat_grads(int count, const float* v_packed, const float* conics,
                           const float* opacity, float* v_xys, float* v_conics, float* v_colors,
                           float* v_opacity, sb_stream_t stream);
@@ -149,26 +157,43 @@ SB_API int sb_unpack_splat_grads(int count, const float* v_packed, const float* 
  * The view loop of rasterize_gaussians_to_multiimgs (gs_utils.py:20-27) with the per-view
  * colour path of gs_utils.py:64-79 folded in; one launch for all V views of a scene.
  *   sh_degree = -1: color_src is (N,3) view-independent rgb (degree-0 path, gs_utils.py:65)
- *   sh_degree 0..4: color_src is (N,K,3) SH coefficients, colour = max(SH(mean - campos_v) + 0.5, 0)
- * opacities (N,) are activated values; campos (V,3) camera centres (may be NULL if sh_degree=-1).
+ *   sh_degree 0..4: colour = max(SH(mean - campos_v) + 0.5, 0); the coefficients are either one
+ *                   (N,K,3) array (color_src, color_rest = NULL) or SplatFormer's own split
+ *                   features_dc (N,3) = color_src and features_rest (N,K-1,3) = color_rest
+ *                   (gs_utils.py:59-60), which removes the torch.cat the reference does per view.
+ * flags (OR of SB_FLAG_*) let the kernels apply the wrapper's activations themselves, so the raw
+ * SplatFormer parameters go in and the gradients w.r.t. the raw parameters come out:
+ *   SB_FLAG_RAW_SCALES     scales are log-scales, scale = exp(raw)              (gs_utils.py:45)
+ *   SB_FLAG_RAW_OPACITIES  opacities are logits, opacity = sigmoid(raw)         (gs_utils.py:54)
+ *   SB_FLAG_COLOR_SIGMOID  sh_degree = -1 only: colour = sigmoid(color_src)     (gs_utils.py:65)
+ *   SB_FLAG_C2W_OPENGL     viewmats holds OpenGL camera-to-world matrices; the kernel forms
+ *                          [R^T | -R^T T] with R <- R diag(1,-1,-1) (gs_utils.py:32-42) and takes
+ *                          the camera centre from the matrix (campos may be NULL)
+ * quats may be un-normalised in every mode (the projection normalises and the backward
+ * differentiates through the normalisation, gs_utils.py:46).
  * Writes the packed raster record (V,N,12) for drawn Gaussians, depths/radii/num_tiles_hit
  * (V,N) for all.  The backward consumes the packed gradient record of sb_rasterize_bwd and
  * writes the per-Gaussian sums over views: v_means (N,3) v_scales (N,3) v_quats (N,4)
- * v_opacities (N,) and v_color_src (same shape as color_src). */
+ * v_opacities (N,) v_color_src / v_color_rest (same shapes as the inputs). */
+#define SB_FLAG_RAW_SCALES 1
+#define SB_FLAG_RAW_OPACITIES 2
+#define SB_FLAG_COLOR_SIGMOID 4
+#define SB_FLAG_C2W_OPENGL 8
 SB_API int sb_views_project_fwd(int num_views, int n, const float* means, const float* scales,
                          float glob_scale, const float* quats, const float* opacities,
-                         const float* color_src, int sh_degree, const float* viewmats,
-                         int viewmat_stride, const float* intrins, float fx, float fy, float cx,
-                         float cy, const float* campos, int img_h, int img_w, int block_width,
-                         float clip_thresh, float* packed, float* depths, int* radii,
-                         int* num_tiles_hit, sb_stream_t stream);
+                         const float* color_src, const float* color_rest, int sh_degree, int flags,
+                         const float* viewmats, int viewmat_stride, const float* intrins, float fx,
+                         float fy, float cx, float cy, const float* campos, int img_h, int img_w,
+                         int block_width, float clip_thresh, float* packed, float* depths,
+                         int* radii, int* num_tiles_hit, sb_stream_t stream);
 SB_API int sb_views_project_bwd(int num_views, int n, const float* means, const float* scales,
-                         float glob_scale, const float* quats, int sh_degree, const float* viewmats,
-                         int viewmat_stride, const float* intrins, float fx, float fy, float cx,
-                         float cy, const float* campos, int img_h, int img_w, int block_width,
-                         float clip_thresh, const float* packed, const float* v_packed,
-                         float* v_means, float* v_scales, float* v_quats, float* v_opacities,
-                         float* v_color_src, sb_stream_t stream);
+                         float glob_scale, const float* quats, int sh_degree, int flags,
+                         const float* viewmats, int viewmat_stride, const float* intrins, float fx,
+                         float fy, float cx, float cy, const float* campos, int img_h, int img_w,
+                         int block_width, float clip_thresh, const float* packed,
+                         const float* v_packed, float* v_means, float* v_scales, float* v_quats,
+                         float* v_opacities, float* v_color_src, float* v_color_rest,
+                         sb_stream_t stream);
 
 #ifdef __cplusplus
 }

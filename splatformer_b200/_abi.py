@@ -17,6 +17,10 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "lib
 _lib: Optional[ctypes.CDLL] = None
 
 P, I, F, S = c_void_p, c_int, c_float, c_size_t
+ABI_VERSION = 2
+
+# input-convention flags of sb_views_project_fwd / _bwd (include/splat_b200.h SB_FLAG_*)
+FLAG_RAW_SCALES, FLAG_RAW_OPACITIES, FLAG_COLOR_SIGMOID, FLAG_C2W_OPENGL = 1, 2, 4, 8
 
 # name -> (restype, argtypes); mirrors include/splat_b200.h one to one
 SIGNATURES = {
@@ -33,11 +37,13 @@ SIGNATURES = {
     "sb_sort_pairs": (I, [I, I, P, P, P, P, P, S, P]),
     "sb_tile_bin_edges": (I, [I, P, I, P, P]),
     "sb_pack_splats": (I, [I, P, P, P, P, P, P]),
-    "sb_rasterize_fwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, I, P]),
-    "sb_rasterize_bwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, P, P]),
+    "sb_rasterize_fwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, I, P, I, P, P]),
+    "sb_rasterize_bwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, I, P, I, P, P, P]),
     "sb_unpack_splat_grads": (I, [I, P, P, P, P, P, P, P, P]),
-    "sb_views_project_fwd": (I, [I, I, P, P, F, P, P, P, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P, P]),
-    "sb_views_project_bwd": (I, [I, I, P, P, F, P, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P, P, P, P, P]),
+    "sb_views_project_fwd": (I, [I, I, P, P, F, P, P, P, P, I, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P,
+                                 P]),
+    "sb_views_project_bwd": (I, [I, I, P, P, F, P, I, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P, P, P, P,
+                                 P, P]),
 }
 
 # number of ABI calls that enqueued device work since import (bench.py reports it as gpu_launches)
@@ -61,8 +67,8 @@ def load() -> ctypes.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export it
         fn.restype = res
         fn.argtypes = args
-    if lib.sb_abi_version() != 1:
-        raise ImportError(f"libsplat_b200.so ABI version {lib.sb_abi_version()} != 1; rebuild")
+    if lib.sb_abi_version() != ABI_VERSION:
+        raise ImportError(f"libsplat_b200.so ABI version {lib.sb_abi_version()} != {ABI_VERSION}; rebuild")
     _lib = lib
     return lib
 

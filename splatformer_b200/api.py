@@ -191,8 +191,8 @@ class _RasterizeGaussians(Function):
             1, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
             _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
             img_width, block_width, None, _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
-            _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"), 0, _abi.stream()),
-            "sb_rasterize_fwd")
+            _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"), 0, None, 0, None,
+            _abi.stream()), "sb_rasterize_fwd")
         ctx.empty = False
         ctx.num_intersects = num_intersects
         ctx.meta = (n, img_height, img_width, block_width)
@@ -219,7 +219,7 @@ class _RasterizeGaussians(Function):
             1, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
             _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
             img_width, block_width, _abi.ptr(final_ts, F32, "final_Ts"), _abi.ptr(final_idx, I32, "final_idx"),
-            _abi.ptr(v_out_img, F32, "v_out_img"), _abi.ptr(v_out_alpha, F32, "v_out_alpha"), None,
+            _abi.ptr(v_out_img, F32, "v_out_img"), _abi.ptr(v_out_alpha, F32, "v_out_alpha"), None, 0, None, 0, None,
             _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_bwd")
         v_xys = torch.empty(n, 2, dtype=F32, device=dev)
         v_conics = torch.empty(n, 3, dtype=F32, device=dev)

@@ -104,10 +104,11 @@ constexpr int kViewsBwdBlock = 128;
 template <int DEG>
 __global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
     int num_views, int n, const float* __restrict__ means, const float* __restrict__ scales, float glob,
-    const float* __restrict__ quats, CamSrc cams, const float* __restrict__ campos, int img_h, int img_w,
-    int bw, float clip, int k3_store, const float4* __restrict__ packed,
+    const float* __restrict__ quats, int flags, CamSrc cams, const float* __restrict__ campos, int img_h,
+    int img_w, int bw, float clip, int k3_store, const float4* __restrict__ packed,
     const float4* __restrict__ v_packed, float* __restrict__ v_means, float* __restrict__ v_scales,
-    float* __restrict__ v_quats, float* __restrict__ v_opacities, float* __restrict__ v_color_src) {
+    float* __restrict__ v_quats, float* __restrict__ v_opacities, float* __restrict__ v_color_src,
+    float* __restrict__ v_color_rest) {
   extern __shared__ float smem[];
   constexpr int KU = DEG < 0 ? 1 : (DEG + 1) * (DEG + 1);
   const int g0 = blockIdx.x * kViewsBwdBlock;
@@ -119,10 +120,12 @@ __global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
   for (int i = 0; i < KU * 3; ++i) acc[i] = 0.f;
   if (active) {
     const float m[3] = {__ldg(means + 3 * g), __ldg(means + 3 * g + 1), __ldg(means + 3 * g + 2)};
-    const float s[3] = {__ldg(scales + 3 * g), __ldg(scales + 3 * g + 1), __ldg(scales + 3 * g + 2)};
+    float s[3] = {__ldg(scales + 3 * g), __ldg(scales + 3 * g + 1), __ldg(scales + 3 * g + 2)};
+    if (flags & kFlagRawScales) { s[0] = expf(s[0]); s[1] = expf(s[1]); s[2] = expf(s[2]); }
     const float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
     const float q[4] = {q4.x, q4.y, q4.z, q4.w};
     float am[3] = {0, 0, 0}, as[3] = {0, 0, 0}, aq[4] = {0, 0, 0, 0}, aop = 0.f;
+    float op = 0.f, col0 = 0.f, col1 = 0.f, col2 = 0.f;
     for (int v = 0; v < num_views; ++v) {
       const Cam cam = load_cam(cams, v);
       ProjFwd f;
@@ -132,7 +135,7 @@ __global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
       const float4 ga = __ldg(v_packed + 3 * i), gb = __ldg(v_packed + 3 * i + 1), gc = __ldg(v_packed + 3 * i + 2);
       float vm[3], vs[3], vq[4];
       const float4 col = __ldg(packed + 3 * i + 2);       // r, g, b (after the clamp), opacity
-      const float op = col.w;
+      op = col.w; col0 = col.x; col1 = col.y; col2 = col.z;
       float vx, vy, vca, vcb, vcc, vop;
       moments_to_grads(ga, gb, f.ca, f.cb, f.cc, op, vx, vy, vca, vcb, vcc, vop);
       project_bwd_one(m, s, glob, cam, f, vx, vy, 0.f, vca, vcb, vcc, 0.f, nullptr, vm, vs, vq, nullptr);
@@ -145,13 +148,20 @@ __global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
       if (DEG >= 0) {
         // clamp(x + 0.5, min 0): gradient passes where > 0
         vr = col.x > 0.f ? vr : 0.f; vg = col.y > 0.f ? vg : 0.f; vb = col.z > 0.f ? vb : 0.f;
-        float Y[KU];
-        sh_basis(DEG, m[0] - __ldg(campos + 3 * v), m[1] - __ldg(campos + 3 * v + 1), m[2] - __ldg(campos + 3 * v + 2), Y);
+        float Y[KU], cp[3];
+        load_campos(cams, campos, v, cp);
+        sh_basis(DEG, m[0] - cp[0], m[1] - cp[1], m[2] - cp[2], Y);
 #pragma unroll
         for (int k = 0; k < KU; ++k) { acc[3 * k] += Y[k] * vr; acc[3 * k + 1] += Y[k] * vg; acc[3 * k + 2] += Y[k] * vb; }
       } else {
         acc[0] += vr; acc[1] += vg; acc[2] += vb;
       }
+    }
+    // chain rule through the activations the kernel applied itself (gs_utils.py:45,54,65)
+    if (flags & kFlagRawScales) { as[0] *= s[0]; as[1] *= s[1]; as[2] *= s[2]; }
+    if (flags & kFlagRawOpacities) aop *= op * (1.0f - op);
+    if (DEG < 0 && (flags & kFlagColorSigmoid)) {
+      acc[0] *= col0 * (1.0f - col0); acc[1] *= col1 * (1.0f - col1); acc[2] *= col2 * (1.0f - col2);
     }
 #pragma unroll
     for (int k = 0; k < 3; ++k) { v_means[3 * g + k] = am[k]; v_scales[3 * g + k] = as[k]; }
@@ -166,7 +176,12 @@ __global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
       for (int i = 0; i < KU * 3; ++i) smem[threadIdx.x * row + i] = acc[i];
     }
     __syncthreads();
-    stage_rows_out(smem, v_color_src + (size_t)g0 * k3_store, nb, k3_store, kViewsBwdBlock);
+    if (v_color_rest) {
+      stage_rows_out(smem, v_color_src + (size_t)g0 * 3, nb, 3, kViewsBwdBlock, row, 0);
+      if (k3_store > 3) stage_rows_out(smem, v_color_rest + (size_t)g0 * (k3_store - 3), nb, k3_store - 3, kViewsBwdBlock, row, 3);
+    } else {
+      stage_rows_out(smem, v_color_src + (size_t)g0 * k3_store, nb, k3_store, kViewsBwdBlock, row, 0);
+    }
   }
 }
 
@@ -182,7 +197,7 @@ extern "C" int sb_project_bwd(int num_views, int n, const float* means, const fl
                               float* v_viewmats, sb_stream_t stream) {
   if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16) return SB_ERR_BAD_ARG;
   if (n == 0) return 0;
-  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy};
+  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, 0};
   dim3 grid(sb::ceil_div(n, sb::kProjBwdBlock));
   cudaStream_t st = (cudaStream_t)stream;
   if (v_viewmats)
@@ -197,18 +212,19 @@ extern "C" int sb_project_bwd(int num_views, int n, const float* means, const fl
 }
 
 extern "C" int sb_views_project_bwd(int num_views, int n, const float* means, const float* scales,
-                                    float glob_scale, const float* quats, int sh_degree,
+                                    float glob_scale, const float* quats, int sh_degree, int flags,
                                     const float* viewmats, int viewmat_stride, const float* intrins,
                                     float fx, float fy, float cx, float cy, const float* campos,
                                     int img_h, int img_w, int block_width, float clip_thresh,
                                     const float* packed, const float* v_packed, float* v_means,
                                     float* v_scales, float* v_quats, float* v_opacities,
-                                    float* v_color_src, sb_stream_t stream) {
+                                    float* v_color_src, float* v_color_rest, sb_stream_t stream) {
+  const bool c2w = flags & sb::kFlagC2wOpenGL;
   if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || sh_degree < -1 || sh_degree > 4 ||
-      (sh_degree >= 0 && !campos))
+      (sh_degree >= 0 && !campos && !c2w) || (sh_degree < 0 && v_color_rest))
     return SB_ERR_BAD_ARG;
   if (n == 0) return 0;
-  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy};
+  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0};
   const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
   const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsBwdBlock * (k3 | 1) * sizeof(float);
   dim3 grid(sb::ceil_div(n, sb::kViewsBwdBlock));
@@ -218,8 +234,9 @@ extern "C" int sb_views_project_bwd(int num_views, int n, const float* means, co
 #define SB_CASE(D)                                                                                   \
   case D:                                                                                            \
     sb::views_project_bwd_kernel<D><<<grid, sb::kViewsBwdBlock, smem, st>>>(                         \
-        num_views, n, means, scales, glob_scale, quats, cams, campos, img_h, img_w, block_width,     \
-        clip_thresh, k3, pk, vpk, v_means, v_scales, v_quats, v_opacities, v_color_src);             \
+        num_views, n, means, scales, glob_scale, quats, flags, cams, campos, img_h, img_w,           \
+        block_width, clip_thresh, k3, pk, vpk, v_means, v_scales, v_quats, v_opacities, v_color_src, \
+        v_color_rest);                                                                               \
     break;
   switch (sh_degree) { SB_CASE(-1) SB_CASE(0) SB_CASE(1) SB_CASE(2) SB_CASE(3) SB_CASE(4) }
 #undef SB_CASE

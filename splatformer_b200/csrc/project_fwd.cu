@@ -47,7 +47,10 @@ __global__ void __launch_bounds__(kProjBlock) project_fwd_kernel(
 // cameras, writing the packed 48-byte raster record, depth, radius and tile count per view.
 // Coefficients are read from HBM once per scene instead of once per view.
 //   DEG = -1 : color_src is (N,3) view-independent rgb (SplatFormer's degree-0 path, :65)
-//   DEG >= 0 : color_src is (N,K,3) SH coefficients; colour = max(SH(dir) + 0.5, 0)  (:78-79)
+//   DEG >= 0 : colour = max(SH(dir) + 0.5, 0)  (:78-79); the coefficients are either one (N,K,3)
+//              array (color_src, color_rest = NULL) or features_dc (N,3) + features_rest (N,K-1,3)
+//              as SplatFormer stores them (:59-60), staged side by side without a concatenation.
+// `flags` (sb_common.cuh) select raw inputs: log-scales, opacity logits, sigmoid colours, c2w cameras.
 // ------------------------------------------------------------------------------------------------
 constexpr int kViewsBlock = 128;
 
@@ -55,16 +58,23 @@ template <int DEG>
 __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     int num_views, int n, const float* __restrict__ means, const float* __restrict__ scales, float glob,
     const float* __restrict__ quats, const float* __restrict__ opacities,
-    const float* __restrict__ color_src, int k3_store, CamSrc cams, const float* __restrict__ campos,
-    int img_h, int img_w, int bw, float clip, float4* __restrict__ packed, float* __restrict__ depths,
-    int* __restrict__ radii, int* __restrict__ tiles) {
+    const float* __restrict__ color_src, const float* __restrict__ color_rest, int k3_store, int flags,
+    CamSrc cams, const float* __restrict__ campos, int img_h, int img_w, int bw, float clip,
+    float4* __restrict__ packed, float* __restrict__ depths, int* __restrict__ radii,
+    int* __restrict__ tiles) {
   extern __shared__ float smem[];
   constexpr int KU = DEG < 0 ? 1 : (DEG + 1) * (DEG + 1);
   const int g0 = blockIdx.x * kViewsBlock;
   const int nb = min(kViewsBlock, n - g0);
   float c[KU * 3];
   if (DEG >= 0) {
-    stage_rows_in(smem, color_src + (size_t)g0 * k3_store, nb, k3_store, kViewsBlock);
+    const int row = padded_row(k3_store);
+    if (color_rest) {
+      stage_rows_in(smem, color_src + (size_t)g0 * 3, nb, 3, kViewsBlock, row, 0);
+      if (k3_store > 3) stage_rows_in(smem, color_rest + (size_t)g0 * (k3_store - 3), nb, k3_store - 3, kViewsBlock, row, 3);
+    } else {
+      stage_rows_in(smem, color_src + (size_t)g0 * k3_store, nb, k3_store, kViewsBlock, row, 0);
+    }
     __syncthreads();
   }
   const int g = g0 + threadIdx.x;
@@ -75,12 +85,15 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     for (int i = 0; i < KU * 3; ++i) c[i] = smem[threadIdx.x * row + i];
   } else {
     c[0] = __ldg(color_src + 3 * g); c[1] = __ldg(color_src + 3 * g + 1); c[2] = __ldg(color_src + 3 * g + 2);
+    if (flags & kFlagColorSigmoid) { c[0] = sigmoidf_(c[0]); c[1] = sigmoidf_(c[1]); c[2] = sigmoidf_(c[2]); }
   }
   const float m[3] = {__ldg(means + 3 * g), __ldg(means + 3 * g + 1), __ldg(means + 3 * g + 2)};
-  const float s[3] = {__ldg(scales + 3 * g), __ldg(scales + 3 * g + 1), __ldg(scales + 3 * g + 2)};
+  float s[3] = {__ldg(scales + 3 * g), __ldg(scales + 3 * g + 1), __ldg(scales + 3 * g + 2)};
+  if (flags & kFlagRawScales) { s[0] = expf(s[0]); s[1] = expf(s[1]); s[2] = expf(s[2]); }
   const float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
   const float q[4] = {q4.x, q4.y, q4.z, q4.w};
-  const float op = __ldg(opacities + g);
+  float op = __ldg(opacities + g);
+  if (flags & kFlagRawOpacities) op = sigmoidf_(op);
   for (int v = 0; v < num_views; ++v) {
     const Cam cam = load_cam(cams, v);
     ProjFwd o;
@@ -92,8 +105,9 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     if (!o.valid) continue;     // packed record of a culled Gaussian is never read
     float r, gg, b;
     if (DEG >= 0) {
-      float Y[KU];
-      sh_basis(DEG, m[0] - __ldg(campos + 3 * v), m[1] - __ldg(campos + 3 * v + 1), m[2] - __ldg(campos + 3 * v + 2), Y);
+      float Y[KU], cp[3];
+      load_campos(cams, campos, v, cp);
+      sh_basis(DEG, m[0] - cp[0], m[1] - cp[1], m[2] - cp[2], Y);
       r = 0.f; gg = 0.f; b = 0.f;
 #pragma unroll
       for (int k = 0; k < KU; ++k) { r += Y[k] * c[3 * k]; gg += Y[k] * c[3 * k + 1]; b += Y[k] * c[3 * k + 2]; }
@@ -118,7 +132,7 @@ extern "C" int sb_project_fwd(int num_views, int n, const float* means, const fl
   if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || img_h < 1 || img_w < 1)
     return SB_ERR_BAD_ARG;
   if (n == 0) return 0;
-  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy};
+  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, 0};
   dim3 grid(sb::ceil_div(n, sb::kProjBlock), num_views);
   sb::project_fwd_kernel<<<grid, sb::kProjBlock, 0, (cudaStream_t)stream>>>(
       n, means, scales, glob_scale, quats, cams, img_h, img_w, block_width, clip_thresh, xys, depths,
@@ -128,26 +142,29 @@ extern "C" int sb_project_fwd(int num_views, int n, const float* means, const fl
 
 extern "C" int sb_views_project_fwd(int num_views, int n, const float* means, const float* scales,
                                     float glob_scale, const float* quats, const float* opacities,
-                                    const float* color_src, int sh_degree, const float* viewmats,
-                                    int viewmat_stride, const float* intrins, float fx, float fy,
-                                    float cx, float cy, const float* campos, int img_h, int img_w,
-                                    int block_width, float clip_thresh, float* packed, float* depths,
-                                    int* radii, int* num_tiles_hit, sb_stream_t stream) {
+                                    const float* color_src, const float* color_rest, int sh_degree,
+                                    int flags, const float* viewmats, int viewmat_stride,
+                                    const float* intrins, float fx, float fy, float cx, float cy,
+                                    const float* campos, int img_h, int img_w, int block_width,
+                                    float clip_thresh, float* packed, float* depths, int* radii,
+                                    int* num_tiles_hit, sb_stream_t stream) {
+  const bool c2w = flags & sb::kFlagC2wOpenGL;
   if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || img_h < 1 || img_w < 1 ||
-      sh_degree < -1 || sh_degree > 4 || (sh_degree >= 0 && !campos))
+      sh_degree < -1 || sh_degree > 4 || (sh_degree >= 0 && !campos && !c2w) || (sh_degree < 0 && color_rest) ||
+      ((flags & sb::kFlagColorSigmoid) && sh_degree >= 0))
     return SB_ERR_BAD_ARG;
   if (n == 0) return 0;
-  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy};
+  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0};
   const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
   const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsBlock * (k3 | 1) * sizeof(float);
   dim3 grid(sb::ceil_div(n, sb::kViewsBlock));
   cudaStream_t st = (cudaStream_t)stream;
   float4* pk = reinterpret_cast<float4*>(packed);
-#define SB_CASE(D)                                                                                     \
-  case D:                                                                                              \
-    sb::views_project_fwd_kernel<D><<<grid, sb::kViewsBlock, smem, st>>>(                              \
-        num_views, n, means, scales, glob_scale, quats, opacities, color_src, k3, cams, campos, img_h, \
-        img_w, block_width, clip_thresh, pk, depths, radii, num_tiles_hit);                            \
+#define SB_CASE(D)                                                                                       \
+  case D:                                                                                                \
+    sb::views_project_fwd_kernel<D><<<grid, sb::kViewsBlock, smem, st>>>(                                \
+        num_views, n, means, scales, glob_scale, quats, opacities, color_src, color_rest, k3, flags, cams, \
+        campos, img_h, img_w, block_width, clip_thresh, pk, depths, radii, num_tiles_hit);               \
     break;
   switch (sh_degree) { SB_CASE(-1) SB_CASE(0) SB_CASE(1) SB_CASE(2) SB_CASE(3) SB_CASE(4) }
 #undef SB_CASE

@@ -95,10 +95,10 @@ template <bool RECT>
 __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ ids_sorted,
     const int2* __restrict__ tile_bins, const float* __restrict__ background, int tiles_x,
-    int tiles_y, int img_w, int img_h, int bw, const float* __restrict__ final_ts,
+    int tiles_y, int img_w, int img_h, int bw, int clamped, const float* __restrict__ final_ts,
     const int* __restrict__ final_idx, const float* __restrict__ v_out_img,
     const float* __restrict__ v_out_alpha, const float* __restrict__ out_img_clamped,
-    float* __restrict__ v_packed) {
+    const void* __restrict__ gt, int gt_u8, const float* __restrict__ v_loss, float* __restrict__ v_packed) {
   extern __shared__ float4 smem4[];
   float4* sA = smem4;
   float4* sB = sA + kBatch;
@@ -123,9 +123,24 @@ __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
     const size_t pix = ((size_t)v * img_h + pm.py_i) * img_w + pm.px_i;
     T_final = __ldg(final_ts + pix);
     bin_final = __ldg(final_idx + pix);
-    vo_r = __ldg(v_out_img + 3 * pix); vo_g = __ldg(v_out_img + 3 * pix + 1); vo_b = __ldg(v_out_img + 3 * pix + 2);
+    if (v_out_img) {
+      vo_r = __ldg(v_out_img + 3 * pix); vo_g = __ldg(v_out_img + 3 * pix + 1); vo_b = __ldg(v_out_img + 3 * pix + 2);
+    }
     if (v_out_alpha) vo_a = __ldg(v_out_alpha + pix);
-    if (out_img_clamped) {
+    if (gt) {
+      // fused L1 loss (train.py:275): the forward stored the image, d|x - gt|/dx = sign(x - gt),
+      // scaled by the upstream gradient of this view's loss term
+      const float sc = __ldg(v_loss + v);
+      float tr, tg, tb;
+      load_gt(gt, gt_u8, pix, tr, tg, tb);
+      const float dr = __ldg(out_img_clamped + 3 * pix) - tr;
+      const float dg = __ldg(out_img_clamped + 3 * pix + 1) - tg;
+      const float db = __ldg(out_img_clamped + 3 * pix + 2) - tb;
+      vo_r += dr > 0.f ? sc : (dr < 0.f ? -sc : 0.f);
+      vo_g += dg > 0.f ? sc : (dg < 0.f ? -sc : 0.f);
+      vo_b += db > 0.f ? sc : (db < 0.f ? -sc : 0.f);
+    }
+    if (out_img_clamped && clamped) {
       // the forward stored min(rgb, 1) (gs_utils.py:111): no gradient through a clamped channel
       if (!(__ldg(out_img_clamped + 3 * pix) < 1.0f)) vo_r = 0.f;
       if (!(__ldg(out_img_clamped + 3 * pix + 1) < 1.0f)) vo_g = 0.f;
@@ -205,9 +220,12 @@ extern "C" int sb_rasterize_bwd(int num_views, int n, const float* packed,
                                 const int* gaussian_ids_sorted, const int* tile_bins,
                                 const float* background, int img_h, int img_w, int block_width,
                                 const float* final_ts, const int* final_idx, const float* v_out_img,
-                                const float* v_out_alpha, const float* out_img_clamped,
+                                const float* v_out_alpha, const float* out_img,
+                                int clamped_rgb_max1, const void* gt, int gt_is_u8,
+                                const float* v_loss,
                                 float* v_packed, sb_stream_t stream) {
-  if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || block_width < 2 || block_width > 16)
+  if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || block_width < 2 || block_width > 16 ||
+      (!v_out_img && !gt && !v_out_alpha) || (gt && (!out_img || !v_loss)) || (clamped_rgb_max1 && !out_img))
     return SB_ERR_BAD_ARG;
   const int tiles_x = sb::ceil_div(img_w, block_width), tiles_y = sb::ceil_div(img_h, block_width);
   dim3 grid(tiles_x * tiles_y, num_views);
@@ -218,7 +236,7 @@ extern "C" int sb_rasterize_bwd(int num_views, int n, const float* packed,
   sb::raster_bwd_kernel<RECT><<<grid, sb::kRasterBlock, sb::kBwdSmem, (cudaStream_t)stream>>>(            \
       n, reinterpret_cast<const float4*>(packed), gaussian_ids_sorted,                                    \
       reinterpret_cast<const int2*>(tile_bins), background, tiles_x, tiles_y, img_w, img_h, block_width,  \
-      final_ts, final_idx, v_out_img, v_out_alpha, out_img_clamped, v_packed)
+      clamped_rgb_max1, final_ts, final_idx, v_out_img, v_out_alpha, out_img, gt, gt_is_u8, v_loss, v_packed)
   if (block_width == 16) SB_LAUNCH(true); else SB_LAUNCH(false);
 #undef SB_LAUNCH
   SB_RETURN_LAST();

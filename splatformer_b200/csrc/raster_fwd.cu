@@ -18,7 +18,8 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
     const int2* __restrict__ tile_bins, const float* __restrict__ background, int tiles_x,
     int tiles_y, int img_w, int img_h, int bw, const int* __restrict__ cum_tiles_hit,
     float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx,
-    float* __restrict__ out_alpha, int clamp_rgb) {
+    float* __restrict__ out_alpha, int clamp_rgb, const void* __restrict__ gt, int gt_u8,
+    float* __restrict__ loss_partial) {
   __shared__ float4 sAll[2][3][kBatch];          // double-buffered staging: [buffer][record word][slot]
   const int tile = blockIdx.x, v = blockIdx.y;
   const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
@@ -90,27 +91,48 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
     }
   }
   cp_async_wait_all();
+  float l1 = 0.f, l2 = 0.f;
   if (pm.inside) {
     const size_t pix = ((size_t)v * img_h + pm.py_i) * img_w + pm.px_i;
+    bool empty_view = false;
     if (cum_tiles_hit) {
       // upstream quirk: a view without a single intersection reports final_T = 0
       // (alpha = 1) while its image is the plain background
       const int hi = __ldg(cum_tiles_hit + (size_t)(v + 1) * n - 1);
       const int lo = v ? __ldg(cum_tiles_hit + (size_t)v * n - 1) : 0;
-      if (hi - lo < 1) {
-        final_ts[pix] = 0.f; final_idx[pix] = 0;
-        if (out_alpha) out_alpha[pix] = 1.f;
-        out_img[3 * pix] = __ldg(background); out_img[3 * pix + 1] = __ldg(background + 1);
-        out_img[3 * pix + 2] = __ldg(background + 2);
-        return;
-      }
+      empty_view = hi - lo < 1;
     }
-    final_ts[pix] = T;
-    final_idx[pix] = cur_idx;
-    if (out_alpha) out_alpha[pix] = 1.0f - T;
     float r = pr + T * __ldg(background), g = pg + T * __ldg(background + 1), b = pb + T * __ldg(background + 2);
     if (clamp_rgb) { r = fminf(r, 1.0f); g = fminf(g, 1.0f); b = fminf(b, 1.0f); }   // gs_utils.py:111
+    final_ts[pix] = empty_view ? 0.f : T;
+    final_idx[pix] = cur_idx;
+    if (out_alpha) out_alpha[pix] = empty_view ? 1.f : 1.0f - T;
     out_img[3 * pix] = r; out_img[3 * pix + 1] = g; out_img[3 * pix + 2] = b;
+    if (gt) {
+      float tr, tg, tb;
+      load_gt(gt, gt_u8, pix, tr, tg, tb);
+      const float dr = r - tr, dg = g - tg, db = b - tb;
+      l1 = fabsf(dr) + fabsf(dg) + fabsf(db);
+      l2 = dr * dr + dg * dg + db * db;
+    }
+  }
+  if (loss_partial) {
+    // fused L1 / squared-error partial sums of the tile (train.py:275,278): one deterministic
+    // (V, T, 2) entry per CTA, summed by the caller
+    __shared__ float sRed[2][kRasterBlock / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      l1 += __shfl_xor_sync(0xffffffffu, l1, o);
+      l2 += __shfl_xor_sync(0xffffffffu, l2, o);
+    }
+    if (lane == 0) { sRed[0][threadIdx.x >> 5] = l1; sRed[1][threadIdx.x >> 5] = l2; }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < kRasterBlock / 32; ++w) t += sRed[threadIdx.x][w];
+      loss_partial[((size_t)v * tiles_x * tiles_y + tile) * 2 + threadIdx.x] = t;
+    }
   }
 }
 
@@ -121,14 +143,16 @@ extern "C" int sb_rasterize_fwd(int num_views, int n, const float* packed,
                                 const float* background, int img_h, int img_w, int block_width,
                                 const int* cum_tiles_hit, float* out_img, float* final_ts,
                                 int* final_idx, float* out_alpha, int clamp_rgb_max1,
+                                const void* gt, int gt_is_u8, float* loss_partial,
                                 sb_stream_t stream) {
-  if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || block_width < 2 || block_width > 16)
+  if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || block_width < 2 || block_width > 16 ||
+      (loss_partial && !gt))
     return SB_ERR_BAD_ARG;
   const int tiles_x = sb::ceil_div(img_w, block_width), tiles_y = sb::ceil_div(img_h, block_width);
   dim3 grid(tiles_x * tiles_y, num_views);
   sb::raster_fwd_kernel<<<grid, sb::kRasterBlock, 0, (cudaStream_t)stream>>>(
       n, reinterpret_cast<const float4*>(packed), gaussian_ids_sorted,
       reinterpret_cast<const int2*>(tile_bins), background, tiles_x, tiles_y, img_w, img_h, block_width,
-      cum_tiles_hit, out_img, final_ts, final_idx, out_alpha, clamp_rgb_max1);
+      cum_tiles_hit, out_img, final_ts, final_idx, out_alpha, clamp_rgb_max1, gt, gt_is_u8, loss_partial);
   SB_RETURN_LAST();
 }

@@ -17,15 +17,28 @@ struct CamSrc {
   int stride;
   const float* intrins;  // (V,4) or nullptr
   float fx, fy, cx, cy;
+  int c2w_opengl;        // viewmats holds OpenGL camera-to-world matrices (gs_utils.py:32-42 is done here)
 };
 
 __device__ __forceinline__ Cam load_cam(const CamSrc& s, int v) {
   Cam c;
   const float* m = s.viewmats + (size_t)v * s.stride;
+  if (s.c2w_opengl) {
+    // R <- R diag(1,-1,-1); viewmat = [R^T | -R^T T]   (/root/reference/utils/gs_utils.py:32-42)
+    const float t0 = __ldg(m + 3), t1 = __ldg(m + 7), t2 = __ldg(m + 11);
 #pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    c.w[3 * i] = __ldg(m + 4 * i); c.w[3 * i + 1] = __ldg(m + 4 * i + 1); c.w[3 * i + 2] = __ldg(m + 4 * i + 2);
-    c.p[i] = __ldg(m + 4 * i + 3);
+    for (int i = 0; i < 3; ++i) {
+      const float sgn = i == 0 ? 1.0f : -1.0f;
+      const float a = sgn * __ldg(m + i), b = sgn * __ldg(m + 4 + i), d = sgn * __ldg(m + 8 + i);
+      c.w[3 * i] = a; c.w[3 * i + 1] = b; c.w[3 * i + 2] = d;
+      c.p[i] = -(a * t0 + b * t1 + d * t2);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      c.w[3 * i] = __ldg(m + 4 * i); c.w[3 * i + 1] = __ldg(m + 4 * i + 1); c.w[3 * i + 2] = __ldg(m + 4 * i + 2);
+      c.p[i] = __ldg(m + 4 * i + 3);
+    }
   }
   if (s.intrins) {
     const float* k = s.intrins + 4 * v;
@@ -35,5 +48,23 @@ __device__ __forceinline__ Cam load_cam(const CamSrc& s, int v) {
   }
   return c;
 }
+
+// Camera centre of view v (for the SH view direction, gs_utils.py:67-69).
+__device__ __forceinline__ void load_campos(const CamSrc& s, const float* __restrict__ campos, int v, float* out) {
+  if (s.c2w_opengl) {
+    const float* m = s.viewmats + (size_t)v * s.stride;
+    out[0] = __ldg(m + 3); out[1] = __ldg(m + 7); out[2] = __ldg(m + 11);
+  } else {
+    out[0] = __ldg(campos + 3 * v); out[1] = __ldg(campos + 3 * v + 1); out[2] = __ldg(campos + 3 * v + 2);
+  }
+}
+
+// Input-convention flags of the fused multi-view kernels (sb_views_project_fwd / _bwd).
+constexpr int kFlagRawScales = 1;      // scales are log-scales: scale = exp(raw)            (gs_utils.py:45)
+constexpr int kFlagRawOpacities = 2;   // opacities are logits: opacity = sigmoid(raw)       (gs_utils.py:54)
+constexpr int kFlagColorSigmoid = 4;   // sh_degree = -1 only: colour = sigmoid(color_src)   (gs_utils.py:65)
+constexpr int kFlagC2wOpenGL = 8;      // viewmats are OpenGL camera-to-world matrices       (gs_utils.py:32-42)
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 }  // namespace sb

@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(kShBlock) sh_fwd_kernel(int num_views, int n, 
   const int row = padded_row(k3_store);
   const int g0 = blockIdx.x * kShBlock;
   const int nb = min(kShBlock, n - g0);
-  stage_rows_in(smem, coeffs + (size_t)g0 * k3_store, nb, k3_store, kShBlock);
+  stage_rows_in(smem, coeffs + (size_t)g0 * k3_store, nb, k3_store, kShBlock, row);
   __syncthreads();
   const int g = g0 + threadIdx.x;
   if (threadIdx.x >= nb) return;
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(kShBlock) sh_bwd_kernel(int num_views, int n, 
     for (int i = KU * 3; i < k3_store; ++i) smem[threadIdx.x * row + i] = 0.f;
   }
   __syncthreads();
-  stage_rows_out(smem, v_coeffs + (size_t)g0 * k3_store, nb, k3_store, kShBlock);
+  stage_rows_out(smem, v_coeffs + (size_t)g0 * k3_store, nb, k3_store, kShBlock, row);
 }
 
 template <bool FWD>

@@ -9,9 +9,12 @@ __device__ __forceinline__ int padded_row(int k3) { return k3 | 1; }
 
 // global -> shared.  `src` points at the block's first row; rows * k3 floats are contiguous and the
 // span starts 16-byte aligned when (block rows * k3 * 4) % 16 == 0 and the array base is aligned.
+// `row` is the shared-memory row stride and `col0` the first column written, so that two global
+// arrays (features_dc (N,3) and features_rest (N,K-1,3), /root/reference/utils/gs_utils.py:59-60) can be
+// staged side by side into one row without the torch.cat the reference performs per view.
 __device__ __forceinline__ void stage_rows_in(float* smem, const float* __restrict__ src, int rows,
-                                              int k3, int nthreads) {
-  const int row = padded_row(k3);
+                                              int k3, int nthreads, int row, int col0 = 0) {
+  smem += col0;
   const int total = rows * k3;
   const int total4 = total >> 2;
   const float4* src4 = reinterpret_cast<const float4*>(src);
@@ -34,8 +37,8 @@ __device__ __forceinline__ void stage_rows_in(float* smem, const float* __restri
 
 // shared -> global
 __device__ __forceinline__ void stage_rows_out(const float* smem, float* __restrict__ dst, int rows,
-                                               int k3, int nthreads) {
-  const int row = padded_row(k3);
+                                               int k3, int nthreads, int row, int col0 = 0) {
+  smem += col0;
   const int total = rows * k3;
   const int total4 = total >> 2;
   float4* dst4 = reinterpret_cast<float4*>(dst);

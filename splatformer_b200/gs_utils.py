@@ -18,13 +18,16 @@ from typing import Dict, List, Tuple
 import torch
 from torch import Tensor
 
+from . import _abi
 from .render import render_views
 
 BLOCK_WIDTH = 16  # /root/reference/utils/gs_utils.py:12
 
 
 def viewmats_from_c2w(camera_to_worlds: Tensor) -> Tuple[Tensor, Tensor]:
-    """(V,3|4,4) OpenGL camera-to-world -> ((V,3,4) OpenCV world-to-camera, (V,3) camera centres)."""
+    """(V,3|4,4) OpenGL camera-to-world -> ((V,3,4) OpenCV world-to-camera, (V,3) camera centres).
+    The fused path does this inside the projection kernel (FLAG_C2W_OPENGL); this torch version is kept
+    for callers of the per-view API."""
     c2w = camera_to_worlds.to(torch.float32)
     flip = torch.tensor([1.0, -1.0, -1.0], device=c2w.device, dtype=c2w.dtype)
     rot = c2w[:, :3, :3] * flip[None, None, :]          # R @ diag(1,-1,-1)
@@ -35,52 +38,90 @@ def viewmats_from_c2w(camera_to_worlds: Tensor) -> Tuple[Tensor, Tensor]:
     return viewmats.contiguous(), c2w[:, :3, 3].contiguous()
 
 
-def _activate(gs_params: Dict[str, Tensor]):
+def _raw_inputs(gs_params: Dict[str, Tensor]):
+    """Raw SplatFormer parameters -> kernel arguments + flags.  Nothing is activated or concatenated
+    here: exp / normalise / sigmoid (gs_utils.py:45-56), the features_dc | features_rest split (:59-62)
+    and the degree-0 sigmoid colour (:65) are applied inside the projection kernels, and the backward
+    returns gradients w.r.t. these raw tensors directly."""
     gp = {k: (v.float() if v.dtype == torch.half else v) for k, v in gs_params.items()}
-    means = gp["means"]
-    scales = torch.exp(gp["scales"])
-    quats = gp["quats"] / torch.norm(gp["quats"], dim=-1, keepdim=True)
+    flags = _abi.FLAG_RAW_SCALES | _abi.FLAG_C2W_OPENGL
     if "opacities" in gp:
-        opacities = torch.sigmoid(gp["opacities"])
+        opacities, flags = gp["opacities"], flags | _abi.FLAG_RAW_OPACITIES
     elif "opacities_sigmoid" in gp:
         opacities = gp["opacities_sigmoid"]
     else:
         raise ValueError("No opacities found in gs_params")
-    if "features_rest" in gp:
-        colors = torch.cat([gp["features_dc"].unsqueeze(1), gp["features_rest"]], dim=1)
-    else:
-        colors = gp["features_dc"].unsqueeze(1)
-    degree = int(math.sqrt(colors.shape[1]) - 1)
+    dc = gp["features_dc"]
+    rest = gp.get("features_rest")
+    k = 1 + (rest.shape[1] if rest is not None else 0)
+    degree = int(math.sqrt(k) - 1)
     if degree == 0:
-        color_src, sh_degree = torch.sigmoid(colors[:, 0, :]), -1
+        rest, sh_degree, flags = None, -1, flags | _abi.FLAG_COLOR_SIGMOID
     else:
-        color_src, sh_degree = colors, degree
-    return means, scales, quats, opacities, color_src, sh_degree
+        if (degree + 1) ** 2 != k:
+            raise ValueError(f"features_dc + features_rest hold {k} SH bases, not a square number")
+        sh_degree = degree
+    return gp["means"], gp["scales"], gp["quats"], opacities, dc, rest, sh_degree, flags
 
 
 def _scalar(x) -> float:
     return float(x.item()) if isinstance(x, Tensor) else float(x)
 
 
+def _intrinsics(fx, fy, cx, cy, v: int, device) -> Tensor:
+    if all(isinstance(x, Tensor) for x in (fx, fy, cx, cy)):
+        intr = torch.stack([fx.reshape(()), fy.reshape(()), cx.reshape(()), cy.reshape(())]).to(
+            device=device, dtype=torch.float32)                                            # no .item()
+    else:
+        intr = torch.tensor([_scalar(fx), _scalar(fy), _scalar(cx), _scalar(cy)],
+                            dtype=torch.float32).to(device, non_blocking=True)
+    return intr.reshape(1, 4).expand(v, 4).contiguous()
+
+
 def render_scene(gs_params: Dict[str, Tensor], camera_to_worlds: Tensor, cx, cy, fx, fy, width, height,
                  background_color: Tensor, **kwargs) -> Tuple[Tensor, Tensor]:
     """All views at once: rgb (V,H,W,3) clamped to <= 1 and alpha (V,H,W,1)."""
-    means, scales, quats, opacities, color_src, sh_degree = _activate(gs_params)
-    viewmats, campos = viewmats_from_c2w(camera_to_worlds.to(means.device))
-    v = viewmats.shape[0]
+    means, scales, quats, opacities, dc, rest, sh_degree, flags = _raw_inputs(gs_params)
+    c2w = camera_to_worlds.to(means.device)
+    v = c2w.shape[0]
     if isinstance(height, Tensor) and isinstance(width, Tensor) and height.is_cuda:
         h, w = (int(x) for x in torch.stack([height, width]).tolist())     # one sync instead of two
     else:
         h, w = int(_scalar(height)), int(_scalar(width))
-    if all(isinstance(x, Tensor) for x in (fx, fy, cx, cy)):
-        intr = torch.stack([fx, fy, cx, cy]).to(device=means.device, dtype=torch.float32)  # no .item()
-    else:
-        intr = torch.tensor([_scalar(fx), _scalar(fy), _scalar(cx), _scalar(cy)],
-                            dtype=torch.float32).to(means.device, non_blocking=True)
-    intrins = intr.reshape(1, 4).expand(v, 4).contiguous()
-    rgb, alpha = render_views(means, scales, quats, opacities, color_src, sh_degree, viewmats, campos, intrins,
-                              h, w, BLOCK_WIDTH, background=background_color.to(means.device), clamp_rgb=True)
+    intrins = _intrinsics(fx, fy, cx, cy, v, means.device)
+    rgb, alpha = render_views(means, scales, quats, opacities, dc, sh_degree, c2w, None, intrins, h, w,
+                              BLOCK_WIDTH, background=background_color.to(means.device), clamp_rgb=True,
+                              color_rest=rest, flags=flags)
     return rgb, alpha.unsqueeze(-1)
+
+
+def render_l1_loss(gs_params: Dict[str, Tensor], cameras: Dict[str, Tensor], images: Tensor,
+                   return_images: bool = False):
+    """The render loss of SplatFormer's training step in one call (train.py:272-278):
+
+        pred_imgs, _ = rasterize_gaussians_to_multiimgs(out_gs, cameras)
+        for pred, gt in zip(pred_imgs, images): l1 += abs(pred - gt).mean(); psnr(pred, gt)
+
+    images: (V,H,W,3) float32 targets in [0,1] on the device.  Returns (l1 (V,), mse (V,)) -- the
+    per-view means of |pred - gt| (differentiable w.r.t. the raw Gaussian parameters) and of
+    (pred - gt)^2 (for PSNR = -10 log10 mse; not differentiable) -- and the predicted images
+    (V,H,W,3) if return_images.  The image size comes from `images`, so no host synchronisation is
+    spent on cameras['height'/'width']; the loss and its gradient image are computed inside the
+    raster kernels and never exist as tensors."""
+    means, scales, quats, opacities, dc, rest, sh_degree, flags = _raw_inputs(gs_params)
+    if images.dim() != 4 or images.shape[-1] != 3:
+        raise ValueError("images must be (V, H, W, 3)")
+    c2w = cameras["camera_to_worlds"].to(means.device)
+    v, h, w = c2w.shape[0], int(images.shape[1]), int(images.shape[2])
+    if images.shape[0] != v:
+        raise ValueError(f"{images.shape[0]} target images for {v} cameras")
+    intrins = _intrinsics(cameras["fx"], cameras["fy"], cameras["cx"], cameras["cy"], v, means.device)
+    l1_sum, sq_sum, rgb = render_views(means, scales, quats, opacities, dc, sh_degree, c2w, None, intrins, h, w,
+                                       BLOCK_WIDTH, background=cameras["background_color"].to(means.device),
+                                       clamp_rgb=True, color_rest=rest, flags=flags, gt=images)
+    inv = 1.0 / (h * w * 3)
+    out = (l1_sum * inv, sq_sum * inv)
+    return out + (rgb,) if return_images else out
 
 
 def rasterize_gaussians_to_multiimgs(gs_params: Dict[str, Tensor], cameras: Dict[str, Tensor]

@@ -80,10 +80,28 @@ def _c(t: Tensor) -> Tensor:
     return _abi.aligned16(t.contiguous())
 
 
+_side_streams: Dict[int, torch.cuda.Stream] = {}
+
+
+def _side_stream(device) -> torch.cuda.Stream:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _side_streams:
+        _side_streams[idx] = torch.cuda.Stream(device=device)
+    return _side_streams[idx]
+
+
 class _RenderViews(Function):
+    """One autograd node for the whole scene.
+
+    `flags` (see _abi.FLAG_*) tell the kernels which of the wrapper's activations they apply
+    themselves; `color_rest` is features_rest when the SH coefficients arrive split as SplatFormer
+    stores them.  With `gt` given the node returns the per-view L1 and squared-error sums instead of
+    leaving the loss to torch (train.py:275,278) and the backward derives the image gradient inside
+    the raster kernel."""
+
     @staticmethod
-    def forward(ctx, means, scales, quats, opacities, color_src, viewmats, campos, intrins, sh_degree,
-                img_height, img_width, block_width, background, clip_thresh, clamp_rgb):
+    def forward(ctx, means, scales, quats, opacities, color_src, color_rest, viewmats, campos, intrins, gt,
+                sh_degree, flags, img_height, img_width, block_width, background, clip_thresh, clamp_rgb):
         lib = _abi.load()
         dev = means.device
         n = means.shape[0]
@@ -91,11 +109,27 @@ class _RenderViews(Function):
         means, scales, quats = _c(means), _c(scales), _c(quats)
         opacities = _c(opacities).view(-1)
         color_src = _c(color_src)
+        color_rest = None if color_rest is None else _c(color_rest)
         viewmats = _c(viewmats.to(F32))
         vm_stride = viewmats.shape[1] * viewmats.shape[2]
-        campos = _c(campos.to(F32))
+        campos = None if campos is None else _c(campos.to(F32))
         intrins = _c(intrins.to(F32))
         background = _c(background.to(F32))
+        gt_ready = None
+        if gt is not None:
+            if gt.dtype not in (torch.uint8, F32):
+                gt = gt.to(F32)
+            if not gt.is_cuda:
+                # targets in (pinned) host memory: the upload runs on a side stream underneath the
+                # projection / sort stages and is awaited right before the raster kernel needs it
+                side = _side_stream(dev)
+                with torch.cuda.stream(side):
+                    gt = gt.contiguous().to(dev, non_blocking=True)
+                    gt_ready = torch.cuda.Event()
+                    gt_ready.record(side)
+                gt.record_stream(torch.cuda.current_stream())
+            gt = _c(gt)
+        gt_dtype = None if gt is None else gt.dtype
         tiles_x = (img_width + block_width - 1) // block_width
         tiles_y = (img_height + block_width - 1) // block_width
 
@@ -107,9 +141,9 @@ class _RenderViews(Function):
             _abi.check(lib.sb_views_project_fwd(
                 v, n, _abi.ptr(means, F32, "means"), _abi.ptr(scales, F32, "scales"), 1.0,
                 _abi.ptr(quats, F32, "quats"), _abi.ptr(opacities, F32, "opacities"),
-                _abi.ptr(color_src, F32, "color_src"), sh_degree, _abi.ptr(viewmats, F32, "viewmats"),
-                vm_stride, _abi.ptr(intrins, F32, "intrins"), 0.0, 0.0, 0.0, 0.0,
-                _abi.ptr(campos, F32, "campos"), img_height, img_width, block_width, clip_thresh,
+                _abi.ptr(color_src, F32, "color_src"), _abi.ptr(color_rest, F32, "color_rest"), sh_degree, flags,
+                _abi.ptr(viewmats, F32, "viewmats"), vm_stride, _abi.ptr(intrins, F32, "intrins"), 0.0, 0.0, 0.0,
+                0.0, _abi.ptr(campos, F32, "campos"), img_height, img_width, block_width, clip_thresh,
                 _abi.ptr(packed, F32, "packed"), _abi.ptr(depths, F32, "depths"),
                 _abi.ptr(radii, I32, "radii"), _abi.ptr(tiles_hit, I32, "num_tiles_hit"), _abi.stream()),
                 "sb_views_project_fwd")
@@ -120,7 +154,8 @@ class _RenderViews(Function):
         out_img = torch.empty(v, img_height, img_width, 3, dtype=F32, device=dev)
         final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
         final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)
-        out_alpha = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
+        out_alpha = None if gt is not None else torch.empty(v, img_height, img_width, dtype=F32, device=dev)
+        loss_partial = None if gt is None else torch.empty(v, tiles_x * tiles_y, 2, dtype=F32, device=dev)
         with _stage("map_isect"):
             isect_ids, gaussian_ids = _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x,
                                            tiles_y, block_width)
@@ -128,6 +163,8 @@ class _RenderViews(Function):
             isect_sorted, gids_sorted = utils.sort_isects(isect_ids, gaussian_ids, tiles_x * tiles_y * v)
         with _stage("bin_edges"):
             tile_bins = utils.get_tile_bin_edges(num_intersects, isect_sorted, (tiles_x, tiles_y, 1), v)
+        if gt_ready is not None:
+            torch.cuda.current_stream().wait_event(gt_ready)
         with _stage("raster_fwd"):
             _abi.check(lib.sb_rasterize_fwd(
                 v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
@@ -135,27 +172,44 @@ class _RenderViews(Function):
                 img_width, block_width, _abi.ptr(cum, I32, "cum_tiles_hit"), _abi.ptr(out_img, F32, "out_img"),
                 _abi.ptr(final_ts, F32, "final_Ts"),
                 _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
-                1 if clamp_rgb else 0, _abi.stream()), "sb_rasterize_fwd")
-        ctx.meta = (v, n, sh_degree, img_height, img_width, block_width, clip_thresh, vm_stride,
-                    tuple(color_src.shape), num_intersects, clamp_rgb)
+                1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,
+                _abi.ptr(loss_partial, F32, "loss_partial"), _abi.stream()), "sb_rasterize_fwd")
+        ctx.meta = (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride,
+                    tuple(color_src.shape), None if color_rest is None else tuple(color_rest.shape),
+                    num_intersects, clamp_rgb)
+        keep_img = clamp_rgb or gt is not None
         ctx.save_for_backward(means, scales, quats, viewmats, campos, intrins, background, packed,
-                              gids_sorted, tile_bins, final_ts, final_idx, out_img if clamp_rgb else None)
+                              gids_sorted, tile_bins, final_ts, final_idx, out_img if keep_img else None, gt)
         ctx.set_materialize_grads(False)
+        if gt is not None:
+            sums = loss_partial.sum(dim=1)                       # (V, 2): sum |rgb - gt|, sum (rgb - gt)^2
+            l1_sum, sq_sum = sums[:, 0], sums[:, 1]
+            ctx.mark_non_differentiable(sq_sum, out_img)
+            return l1_sum, sq_sum, out_img
         return out_img, out_alpha
 
     @staticmethod
-    def backward(ctx, v_out_img, v_out_alpha):
+    def backward(ctx, *grads):
         lib = _abi.load()
         (means, scales, quats, viewmats, campos, intrins, background, packed, gids_sorted, tile_bins,
-         final_ts, final_idx, out_img_clamped) = ctx.saved_tensors
-        (v, n, sh_degree, img_height, img_width, block_width, clip_thresh, vm_stride, color_shape,
-         num_intersects, clamp_rgb) = ctx.meta
+         final_ts, final_idx, out_img, gt) = ctx.saved_tensors
+        (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride, color_shape,
+         rest_shape, num_intersects, clamp_rgb) = ctx.meta
         dev = means.device
-        if v_out_img is None and v_out_alpha is None:
-            return (None,) * 15
-        v_out_img = torch.zeros(v, img_height, img_width, 3, dtype=F32, device=dev) if v_out_img is None \
-            else _c(v_out_img)
-        v_out_alpha = None if v_out_alpha is None else _c(v_out_alpha)
+        nin = 18
+        if gt is not None:
+            v_l1 = grads[0]
+            if v_l1 is None:
+                return (None,) * nin
+            v_loss = _c(v_l1.to(F32))
+            v_out_img = v_out_alpha = None
+        else:
+            v_out_img, v_out_alpha = grads
+            if v_out_img is None and v_out_alpha is None:
+                return (None,) * nin
+            v_out_img = None if v_out_img is None else _c(v_out_img)
+            v_out_alpha = None if v_out_alpha is None else _c(v_out_alpha)
+            v_loss = None
         with _stage("zero_grads"):
             v_packed = torch.zeros(v, n, 12, dtype=F32, device=dev)
         with _stage("raster_bwd"):
@@ -164,25 +218,27 @@ class _RenderViews(Function):
                 _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
                 img_width, block_width, _abi.ptr(final_ts, F32, "final_Ts"),
                 _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(v_out_img, F32, "v_out_img"),
-                _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(out_img_clamped, F32, "out_img"),
+                _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(out_img, F32, "out_img"),
+                1 if clamp_rgb else 0, _abi.ptr(gt, None if gt is None else gt.dtype, "gt"),
+                1 if (gt is not None and gt.dtype == torch.uint8) else 0, _abi.ptr(v_loss, F32, "v_loss"),
                 _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_bwd")
         v_means = torch.empty(n, 3, dtype=F32, device=dev)
         v_scales = torch.empty(n, 3, dtype=F32, device=dev)
         v_quats = torch.empty(n, 4, dtype=F32, device=dev)
         v_opac = torch.empty(n, 1, dtype=F32, device=dev)
         v_color = torch.empty(color_shape, dtype=F32, device=dev)
+        v_rest = None if rest_shape is None else torch.empty(rest_shape, dtype=F32, device=dev)
         with _stage("project_sh_bwd"):
             _abi.check(lib.sb_views_project_bwd(
                 v, n, _abi.ptr(means, F32, "means"), _abi.ptr(scales, F32, "scales"), 1.0,
-                _abi.ptr(quats, F32, "quats"), sh_degree, _abi.ptr(viewmats, F32, "viewmats"), vm_stride,
+                _abi.ptr(quats, F32, "quats"), sh_degree, flags, _abi.ptr(viewmats, F32, "viewmats"), vm_stride,
                 _abi.ptr(intrins, F32, "intrins"), 0.0, 0.0, 0.0, 0.0, _abi.ptr(campos, F32, "campos"),
                 img_height, img_width, block_width, clip_thresh, _abi.ptr(packed, F32, "packed"),
                 _abi.ptr(v_packed, F32, "v_packed"), _abi.ptr(v_means, F32, "v_means"),
                 _abi.ptr(v_scales, F32, "v_scales"), _abi.ptr(v_quats, F32, "v_quats"),
-                _abi.ptr(v_opac, F32, "v_opacities"), _abi.ptr(v_color, F32, "v_color_src"), _abi.stream()),
-                "sb_views_project_bwd")
-        return (v_means, v_scales, v_quats, v_opac, v_color, None, None, None, None, None, None, None, None,
-                None, None)
+                _abi.ptr(v_opac, F32, "v_opacities"), _abi.ptr(v_color, F32, "v_color_src"),
+                _abi.ptr(v_rest, F32, "v_color_rest"), _abi.stream()), "sb_views_project_bwd")
+        return (v_means, v_scales, v_quats, v_opac, v_color, v_rest) + (None,) * (nin - 6)
 
 
 def _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x, tiles_y, block_width):
@@ -195,23 +251,29 @@ def _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x, tiles_y
 def render_views(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor, color_src: Tensor,
                  sh_degree: int, viewmats: Tensor, campos: Optional[Tensor], intrins: Tensor,
                  img_height: int, img_width: int, block_width: int = 16,
-                 background: Optional[Tensor] = None, clip_thresh: float = 0.01, clamp_rgb: bool = False):
+                 background: Optional[Tensor] = None, clip_thresh: float = 0.01, clamp_rgb: bool = False,
+                 color_rest: Optional[Tensor] = None, flags: int = 0, gt: Optional[Tensor] = None):
     """Render all V views of one scene.
 
-    means (N,3), scales (N,3, activated), quats (N,4, unit), opacities (N,1|N, activated);
-    color_src: (N,K,3) SH coefficients with sh_degree in 0..4 (colour = max(SH + 0.5, 0) as
-    gs_utils.py:78-79) or (N,3) rgb with sh_degree = -1; viewmats (V,3|4,4) world->camera;
-    campos (V,3) camera centres; intrins (V,4) = fx, fy, cx, cy.
-    Returns rgb (V,H,W,3) and alpha (V,H,W).  rgb is not clamped unless clamp_rgb=True, which folds
-    the wrapper's torch.clamp(rgb, max=1) (gs_utils.py:111) into the kernels.  Differentiable in
-    means, scales, quats, opacities and color_src."""
+    means (N,3), scales (N,3), quats (N,4), opacities (N,1|N); activated values unless `flags`
+    (_abi.FLAG_RAW_SCALES | FLAG_RAW_OPACITIES | FLAG_COLOR_SIGMOID) say the kernels apply
+    exp / sigmoid themselves.  color_src: (N,K,3) SH coefficients with sh_degree in 0..4 (colour =
+    max(SH + 0.5, 0) as gs_utils.py:78-79; or features_dc (N,3) with color_rest = features_rest
+    (N,K-1,3)), or (N,3) rgb with sh_degree = -1.  viewmats (V,3|4,4) world->camera with campos (V,3)
+    camera centres, or OpenGL camera-to-world matrices with FLAG_C2W_OPENGL; intrins (V,4) = fx, fy, cx, cy.
+
+    Returns rgb (V,H,W,3) and alpha (V,H,W); rgb is not clamped unless clamp_rgb=True, which folds the
+    wrapper's torch.clamp(rgb, max=1) (gs_utils.py:111) into the kernels.  With gt (V,H,W,3) given it
+    returns instead (l1_sum (V,), sq_sum (V,), rgb): the per-view sums of |rgb - gt| (differentiable)
+    and (rgb - gt)^2 (for PSNR, not differentiable) computed inside the raster kernel.
+    Differentiable in means, scales, quats, opacities, color_src and color_rest."""
     assert 2 <= block_width <= 16, "block_width must be between 2 and 16"
     if not means.is_cuda:
         raise RuntimeError("render_views needs CUDA tensors (there is no CPU path)")
     if background is None:
         background = torch.ones(3, dtype=F32, device=means.device)
-    if campos is None:
+    if campos is None and not (flags & _abi.FLAG_C2W_OPENGL):
         campos = torch.zeros(viewmats.shape[0], 3, dtype=F32, device=means.device)
-    return _RenderViews.apply(means, scales, quats, opacities, color_src, viewmats, campos, intrins,
-                              int(sh_degree), int(img_height), int(img_width), int(block_width), background,
-                              float(clip_thresh), bool(clamp_rgb))
+    return _RenderViews.apply(means, scales, quats, opacities, color_src, color_rest, viewmats, campos, intrins,
+                              gt, int(sh_degree), int(flags), int(img_height), int(img_width), int(block_width),
+                              background, float(clip_thresh), bool(clamp_rgb))

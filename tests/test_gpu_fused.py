@@ -48,10 +48,10 @@ def test_fused_matches_per_view_api(cuda, sb_lib, n, deg, size, views):
     loss_b = 0.0
     for v in range(views):
         rgb, alpha = _per_view_api(raw_b, cams, v, deg, cuda)
-        # forward: same device functions underneath; alpha is bit-identical, colours differ only by
-        # where the view direction is normalised (torch outside vs once inside the fused kernel)
-        assert torch.equal(alpha, alphas[v]), f"view {v}: fused alpha differs from per-view API"
-        assert float((rgb - rgbs[v]).abs().max()) <= 2e-6
+        # forward: same device functions underneath; the fused kernels apply exp / sigmoid / the
+        # camera inversion themselves (expf vs torch.exp: last-bit differences), so not bit-identical
+        assert float((alpha - alphas[v]).abs().max()) <= 1e-5, f"view {v}: fused alpha differs from per-view API"
+        assert float((rgb.detach() - rgbs[v].detach()).abs().max()) <= 1e-5
         loss_b = loss_b + (rgb - gt[v]).abs().mean() + 0.1 * alpha.mean()
     loss_a.backward()
     loss_b.backward()
@@ -99,3 +99,62 @@ def test_fused_single_view_and_empty_view(cuda, sb_lib):
     rgb0, a0 = gs_utils.rasterize_gaussians_to_singleimg(raw, cd["camera_to_worlds"][0], **{
         k_: cd[k_] for k_ in ("cx", "cy", "fx", "fy", "width", "height", "background_color")})
     assert torch.equal(rgb0, rgbs[0]) and torch.equal(a0, alphas[0])
+
+
+@pytest.mark.parametrize("n,deg,size,views,opkey", [(2500, 3, (144, 112), 3, "opacities"),
+                                                    (1500, 0, (80, 96), 2, "opacities"),
+                                                    (1200, 2, (64, 64), 2, "opacities_sigmoid")])
+def test_fused_l1_loss_matches_torch_loss(cuda, sb_lib, n, deg, size, views, opkey):
+    """render_l1_loss (loss + gradient image inside the raster kernels) == torch L1 on render_scene."""
+    gs = synth.shell_scene(n, deg, seed=11, scale_mult=0.3)
+    if opkey == "opacities_sigmoid":
+        gs["opacities_sigmoid"] = torch.sigmoid(gs.pop("opacities"))
+    cams = synth.orbit_cameras(views, size[0], size[1], background=(0.2, 0.4, 0.1))
+    gt = synth.target_images(views, size[1], size[0], seed=5).to(cuda)
+    cams_dev = {k_: v.to(cuda) for k_, v in cams.items()}
+    raw_a = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    raw_b = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    weights = torch.linspace(0.5, 1.5, views, device=cuda)            # unequal upstream gradients per view
+    l1, mse, imgs = gs_utils.render_l1_loss(raw_a, cams_dev, gt, return_images=True)
+    assert l1.shape == (views,) and mse.shape == (views,) and not mse.requires_grad
+    rgb, _ = gs_utils.render_scene(raw_b, **cams_dev)
+    assert torch.equal(imgs, rgb.detach())
+    l1_ref = (rgb - gt).abs().mean(dim=(1, 2, 3))
+    mse_ref = ((rgb - gt) ** 2).mean(dim=(1, 2, 3))
+    assert torch.allclose(l1, l1_ref, rtol=1e-5, atol=1e-7)
+    assert torch.allclose(mse, mse_ref.detach(), rtol=1e-5, atol=1e-7)
+    (l1 * weights).sum().backward()
+    (l1_ref * weights).sum().backward()
+    for name in gs:
+        H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name)
+
+
+def test_fused_l1_loss_matches_oracle(cuda, sb_lib):
+    gs = synth.shell_scene(1800, 1, seed=9, scale_mult=0.3)
+    cams = synth.orbit_cameras(2, 96, 80, background=(0.0, 0.0, 0.0))
+    gt = synth.target_images(2, 80, 96, seed=12)
+    raw = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    raw_ref = {k_: v.clone().requires_grad_() for k_, v in gs.items()}
+    l1, mse = gs_utils.render_l1_loss(raw, {k_: v.to(cuda) for k_, v in cams.items()}, gt.to(cuda))
+    rgbs, _ = R.render_views(raw_ref, cams)
+    l1_ref = torch.stack([(rgb - g).abs().mean() for rgb, g in zip(rgbs, gt)])
+    assert torch.allclose(l1.detach().cpu(), l1_ref.detach(), rtol=1e-4, atol=1e-6)
+    l1.sum().backward(); l1_ref.sum().backward()
+    for name in gs:
+        H.assert_grad_close(raw[name].grad, raw_ref[name].grad, name, rtol=5e-3)
+
+
+def test_fused_l1_loss_uint8_host_targets(cuda, sb_lib):
+    """8-bit targets in pinned host memory (uploaded on a side stream) == float targets on the device."""
+    gs = synth.shell_scene(1500, 2, seed=3, scale_mult=0.3)
+    cams = {k_: v.to(cuda) for k_, v in synth.orbit_cameras(3, 80, 64, background=(0.1, 0.1, 0.1)).items()}
+    gt_u8 = (synth.target_images(3, 64, 80, seed=2) * 255.0).round().to(torch.uint8)
+    raw_a = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    raw_b = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    l1_a, mse_a = gs_utils.render_l1_loss(raw_a, cams, gt_u8.pin_memory())
+    l1_b, mse_b = gs_utils.render_l1_loss(raw_b, cams, gt_u8.to(cuda).float() / 255.0)
+    # the kernel divides by 255 (IEEE), torch multiplies by 1/255: last-bit differences in the targets
+    assert torch.allclose(l1_a, l1_b, rtol=1e-6, atol=0) and torch.allclose(mse_a, mse_b, rtol=1e-6, atol=0)
+    l1_a.sum().backward(); l1_b.sum().backward()
+    for name in gs:
+        H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name)

@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     const float* __restrict__ color_src, const float* __restrict__ color_rest, int k3_store, int flags,
     CamSrc cams, const float* __restrict__ campos, int img_h, int img_w, int bw, float clip,
     float4* __restrict__ packed, float* __restrict__ depths, int* __restrict__ radii,
-    int* __restrict__ tiles) {
+    int* __restrict__ tiles, int* __restrict__ tile_counts) {
   extern __shared__ float smem[];
   constexpr int KU = DEG < 0 ? 1 : (DEG + 1) * (DEG + 1);
   const int g0 = blockIdx.x * kViewsBlock;
@@ -94,7 +94,11 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
   const float q[4] = {q4.x, q4.y, q4.z, q4.w};
   float op = __ldg(opacities + g);
   if (flags & kFlagRawOpacities) op = sigmoidf_(op);
-  for (int v = 0; v < num_views; ++v) {
+  // blocks start at different views so that, at any moment, the per-tile count reductions of the
+  // resident blocks spread over all V*T counters instead of the T counters of one view
+  const int v0 = blockIdx.x % num_views;
+  for (int vi = 0; vi < num_views; ++vi) {
+    const int v = vi + v0 < num_views ? vi + v0 : vi + v0 - num_views;
     const Cam cam = load_cam(cams, v);
     ProjFwd o;
     project_fwd_one(m, s, glob, q, cam, img_w, img_h, bw, clip, o);
@@ -103,6 +107,13 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     tiles[i] = o.tiles;
     depths[i] = o.depth;
     if (!o.valid) continue;     // packed record of a culled Gaussian is never read
+    if (tile_counts) {
+      // per-tile intersection counts for the counting sort of tile_sort.cu
+      const int tiles_x = (img_w + bw - 1) / bw;
+      int* tc = tile_counts + (size_t)v * tiles_x * ((img_h + bw - 1) / bw);
+      for (int ty = o.min_y; ty < o.max_y; ++ty)
+        for (int tx = o.min_x; tx < o.max_x; ++tx) atomicAdd(tc + ty * tiles_x + tx, 1);
+    }
     float r, gg, b;
     if (DEG >= 0) {
       float Y[KU], cp[3];
@@ -147,7 +158,7 @@ extern "C" int sb_views_project_fwd(int num_views, int n, const float* means, co
                                     const float* intrins, float fx, float fy, float cx, float cy,
                                     const float* campos, int img_h, int img_w, int block_width,
                                     float clip_thresh, float* packed, float* depths, int* radii,
-                                    int* num_tiles_hit, sb_stream_t stream) {
+                                    int* num_tiles_hit, int* tile_counts, sb_stream_t stream) {
   const bool c2w = flags & sb::kFlagC2wOpenGL;
   if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || img_h < 1 || img_w < 1 ||
       sh_degree < -1 || sh_degree > 4 || (sh_degree >= 0 && !campos && !c2w) || (sh_degree < 0 && color_rest) ||
@@ -164,7 +175,7 @@ extern "C" int sb_views_project_fwd(int num_views, int n, const float* means, co
   case D:                                                                                                \
     sb::views_project_fwd_kernel<D><<<grid, sb::kViewsBlock, smem, st>>>(                                \
         num_views, n, means, scales, glob_scale, quats, opacities, color_src, color_rest, k3, flags, cams, \
-        campos, img_h, img_w, block_width, clip_thresh, pk, depths, radii, num_tiles_hit);               \
+        campos, img_h, img_w, block_width, clip_thresh, pk, depths, radii, num_tiles_hit, tile_counts);  \
     break;
   switch (sh_degree) { SB_CASE(-1) SB_CASE(0) SB_CASE(1) SB_CASE(2) SB_CASE(3) SB_CASE(4) }
 #undef SB_CASE

@@ -137,6 +137,9 @@ class _RenderViews(Function):
         depths = torch.empty(v, n, dtype=F32, device=dev)
         radii = torch.empty(v, n, dtype=I32, device=dev)
         tiles_hit = torch.empty(v, n, dtype=I32, device=dev)
+        num_tiles = tiles_x * tiles_y
+        with _stage("zero_counts"):
+            tile_counts = torch.zeros(v * num_tiles, dtype=I32, device=dev)
         with _stage("project_sh_fwd"):
             _abi.check(lib.sb_views_project_fwd(
                 v, n, _abi.ptr(means, F32, "means"), _abi.ptr(scales, F32, "scales"), 1.0,
@@ -145,31 +148,58 @@ class _RenderViews(Function):
                 _abi.ptr(viewmats, F32, "viewmats"), vm_stride, _abi.ptr(intrins, F32, "intrins"), 0.0, 0.0, 0.0,
                 0.0, _abi.ptr(campos, F32, "campos"), img_height, img_width, block_width, clip_thresh,
                 _abi.ptr(packed, F32, "packed"), _abi.ptr(depths, F32, "depths"),
-                _abi.ptr(radii, I32, "radii"), _abi.ptr(tiles_hit, I32, "num_tiles_hit"), _abi.stream()),
-                "sb_views_project_fwd")
-        with _stage("cumsum"):
-            num_intersects, cum = utils.compute_cumulative_intersects(tiles_hit)
+                _abi.ptr(radii, I32, "radii"), _abi.ptr(tiles_hit, I32, "num_tiles_hit"),
+                _abi.ptr(tile_counts, I32, "tile_counts"), _abi.stream()), "sb_views_project_fwd")
+        tile_bins = torch.empty(v * num_tiles, 2, dtype=I32, device=dev)
+        view_end = torch.empty(v, dtype=I32, device=dev)
+        totals = torch.empty(2, dtype=I32, device=dev)
+        with _stage("tile_offsets"):
+            _abi.check(lib.sb_tile_offsets(v, num_tiles, _abi.ptr(tile_counts, I32, "tile_counts"),
+                                           _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(totals, I32, "totals"),
+                                           _abi.ptr(view_end, I32, "view_isect_end"), _abi.stream()),
+                       "sb_tile_offsets")
+            # the one host synchronisation of the scene: sizes the intersection buffers
+            num_intersects, max_tile_count = (int(x) for x in totals.tolist())
         global _last_num_intersects
         _last_num_intersects = num_intersects
         out_img = torch.empty(v, img_height, img_width, 3, dtype=F32, device=dev)
         final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
         final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)
         out_alpha = None if gt is not None else torch.empty(v, img_height, img_width, dtype=F32, device=dev)
-        loss_partial = None if gt is None else torch.empty(v, tiles_x * tiles_y, 2, dtype=F32, device=dev)
-        with _stage("map_isect"):
-            isect_ids, gaussian_ids = _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x,
-                                           tiles_y, block_width)
-        with _stage("sort"):
-            isect_sorted, gids_sorted = utils.sort_isects(isect_ids, gaussian_ids, tiles_x * tiles_y * v)
-        with _stage("bin_edges"):
-            tile_bins = utils.get_tile_bin_edges(num_intersects, isect_sorted, (tiles_x, tiles_y, 1), v)
+        loss_partial = None if gt is None else torch.empty(v, num_tiles, 2, dtype=F32, device=dev)
+        if max_tile_count <= lib.sb_tile_sort_capacity():
+            # counting sort by tile + per-tile (depth, id) sort in shared memory (csrc/tile_sort.cu)
+            keys = torch.empty(max(num_intersects, 1), dtype=torch.int64, device=dev)
+            gids_sorted = torch.empty(max(num_intersects, 1), dtype=I32, device=dev)
+            with _stage("scatter_isects"):
+                _abi.check(lib.sb_scatter_isects(
+                    v, n, _abi.ptr(packed, F32, "packed"), 12, _abi.ptr(depths, F32, "depths"),
+                    _abi.ptr(radii, I32, "radii"), tiles_x, tiles_y, block_width,
+                    _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(tile_counts, I32, "tile_counts"),
+                    _abi.ptr(keys, torch.int64, "isect_keys"), _abi.stream()), "sb_scatter_isects")
+            with _stage("sort_tiles"):
+                _abi.check(lib.sb_sort_tiles(v * num_tiles, max_tile_count, _abi.ptr(tile_bins, I32, "tile_bins"),
+                                             _abi.ptr(keys, torch.int64, "isect_keys"),
+                                             _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"), _abi.stream()),
+                           "sb_sort_tiles")
+        else:
+            # very deep tiles: global 64-bit (tile | depth) radix sort, as the per-view API does
+            with _stage("cumsum"):
+                _, cum = utils.compute_cumulative_intersects(tiles_hit, sync=False)
+            with _stage("map_isect"):
+                isect_ids, gaussian_ids = _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x,
+                                               tiles_y, block_width)
+            with _stage("sort"):
+                isect_sorted, gids_sorted = utils.sort_isects(isect_ids, gaussian_ids, num_tiles * v)
+            with _stage("bin_edges"):
+                tile_bins = utils.get_tile_bin_edges(num_intersects, isect_sorted, (tiles_x, tiles_y, 1), v)
         if gt_ready is not None:
             torch.cuda.current_stream().wait_event(gt_ready)
         with _stage("raster_fwd"):
             _abi.check(lib.sb_rasterize_fwd(
                 v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
                 _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
-                img_width, block_width, _abi.ptr(cum, I32, "cum_tiles_hit"), _abi.ptr(out_img, F32, "out_img"),
+                img_width, block_width, _abi.ptr(view_end, I32, "view_isect_end"), _abi.ptr(out_img, F32, "out_img"),
                 _abi.ptr(final_ts, F32, "final_Ts"),
                 _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
                 1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,

@@ -15,9 +15,10 @@ def _scratch(nbytes: int, device) -> Tensor:
     return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)
 
 
-def compute_cumulative_intersects(num_tiles_hit: Tensor) -> Tuple[int, Tensor]:
+def compute_cumulative_intersects(num_tiles_hit: Tensor, sync: bool = True) -> Tuple[int, Tensor]:
     """Inclusive int32 prefix sum of the per-Gaussian tile counts and its last element.
-    The `.item()` is the one host synchronisation upstream has here as well."""
+    The `.item()` is the one host synchronisation upstream has here as well (sync=False skips it and
+    returns -1 for callers that already know the count)."""
     lib = _abi.load()
     flat = num_tiles_hit.contiguous().view(-1)
     cum = torch.empty_like(flat)
@@ -29,7 +30,7 @@ def compute_cumulative_intersects(num_tiles_hit: Tensor) -> Tuple[int, Tensor]:
                                  _abi.ptr(cum, torch.int32, "cum_tiles_hit"),
                                  _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()),
                "sb_cumsum_i32")
-    return int(cum[-1].item()), cum
+    return (int(cum[-1].item()) if sync else -1), cum
 
 
 def map_gaussian_to_intersects(num_points: int, num_intersects: int, xys: Tensor, depths: Tensor,

@@ -123,8 +123,8 @@ SB_API int sb_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted
  *   (pixel, Gaussian) pair, M0 = sum w, M1x = sum w*dx, ... M2yy = sum w*dy*dy.
  *   sb_unpack_splat_grads turns them into the API gradients: v_xy = (a*M1x + b*M1y,
  *   b*M1x + c*M1y), v_conic = (M2xx/2, M2xy, M2yy/2), v_opacity = -M0/opacity.
- * view_isect_end ((V,) intersections of views 0..v, may be NULL): when given, a view without a
- * single intersection gets out_img = background and final_T = 0 (alpha 1) -- the behaviour of
+ * view_has_isects ((V,) int32 flags, may be NULL): when given, a view whose flag is 0 (not a
+ * single intersection) gets out_img = background and final_T = 0 (alpha 1) -- the behaviour of
  * upstream's `num_intersects < 1` early return, applied per view on the device.
  * out_alpha (may be NULL) receives 1 - final_T.  clamp_rgb_max1 != 0 stores min(rgb, 1) -- the
  * wrapper's final clamp (gs_utils.py:111) folded into the kernel; the backward then takes that
@@ -140,7 +140,7 @@ SB_API int sb_pack_splats(int count, const float* xys, const float* conics, cons
                    const float* opacity, float* packed, sb_stream_t stream);
 SB_API int sb_rasterize_fwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
                      const int* tile_bins, const float* background, int img_h, int img_w,
-                     int block_width, const int* view_isect_end, float* out_img, float* final_ts,
+                     int block_width, const int* view_has_isects, float* out_img, float* final_ts,
                      int* final_idx, float* out_alpha, int clamp_rgb_max1, const void* gt,
                      int gt_is_u8, float* loss_partial, sb_stream_t stream);
 SB_API int sb_rasterize_bwd(int num_views, int n, const float* packed, const int* gaussian_ids_sorted,
@@ -153,25 +153,22 @@ SB_API int sb_unpack_splat_grads(int count, const float* v_packed, const float* 
                           const float* opacity, float* v_xys, float* v_conics, float* v_colors,
                           float* v_opacity, sb_stream_t stream);
 
-/* ---- a5-a9 for the fused path: counting sort by tile + per-tile depth sort ---------------
- * Same gaussian_ids_sorted / tile_bins as sb_map_gaussian_to_intersects + sb_sort_pairs +
- * sb_tile_bin_edges (within a tile: ascending depth bits, ties by ascending Gaussian id = the
- * stable sort's emission order), without the 64-bit global radix sort.  Usable when no tile holds
- * more than sb_tile_sort_capacity() Gaussians (totals[1] tells); otherwise use the chain above.
- *   sb_tile_offsets   exclusive scan of tile_counts (V*T) -> tile_bins (V*T,2), totals[0] = number of
- *                     intersections, totals[1] = largest tile count, view_isect_end (V,)
- *   sb_scatter_isects writes (depth bits << 32 | gaussian id) of every intersection into its tile's
- *                     segment of isect_keys (I,); tile_counts is consumed (counted down to zero)
- *   sb_sort_tiles     sorts every segment and writes gaussian_ids_sorted (I,) */
+/* ---- a5-a9 for the fused path: fixed-capacity tile segments + per-tile depth sort ---------
+ * Same per-tile order as sb_map_gaussian_to_intersects + sb_sort_pairs + sb_tile_bin_edges
+ * (ascending depth bits, ties by ascending Gaussian id = the stable sort's emission order) without
+ * the scan, the host read of the intersection count and the 64-bit global radix sort.
+ * sb_views_project_fwd, given tile_counts (V*T, zero-filled) and tile_keys (V*T*tile_capacity),
+ * drops (depth bits << 32 | gaussian id) of every intersection into slot atomicAdd(count) of its
+ * tile's segment [tile*capacity, (tile+1)*capacity).  sb_sort_tiles then sorts every segment and
+ * writes gaussian_ids_sorted (same V*T*capacity indexing), tile_bins (V*T,2) = segment ranges
+ * ((0,0) for empty tiles), view_has_isects (V, zero-filled by the caller) and totals (2 ints,
+ * zero-filled): [0] = number of intersections, [1] = 1 if a tile held more than tile_capacity
+ * Gaussians (its list is then truncated: the caller must redo the binning with the chain above).
+ * tile_capacity: power of two in [64, sb_tile_sort_capacity()], V*T*capacity < 2^31. */
 SB_API int sb_tile_sort_capacity(void);
-SB_API int sb_tile_offsets(int num_views, int tiles_per_view, const int* tile_counts, int* tile_bins,
-                    int* totals, int* view_isect_end, sb_stream_t stream);
-SB_API int sb_scatter_isects(int num_views, int n, const float* xys, int xys_stride, const float* depths,
-                      const int* radii, int tiles_x, int tiles_y, int block_width,
-                      const int* tile_bins, int* tile_counts, uint64_t* isect_keys,
-                      sb_stream_t stream);
-SB_API int sb_sort_tiles(int num_tiles_total, int max_tile_count, const int* tile_bins,
-                  const uint64_t* isect_keys, int* gaussian_ids_sorted, sb_stream_t stream);
+SB_API int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, const int* tile_counts,
+                  const uint64_t* tile_keys, int* gaussian_ids_sorted, int* tile_bins,
+                  int* view_has_isects, int* totals, sb_stream_t stream);
 
 /* ---- a1 / a2: fused multi-view projection + SH colour ----------------------------------
  * The view loop of rasterize_gaussians_to_multiimgs (gs_utils.py:20-27) with the per-view
@@ -195,8 +192,8 @@ SB_API int sb_sort_tiles(int num_tiles_total, int max_tile_count, const int* til
  * (V,N) for all.  The backward consumes the packed gradient record of sb_rasterize_bwd and
  * writes the per-Gaussian sums over views: v_means (N,3) v_scales (N,3) v_quats (N,4)
  * v_opacities (N,) v_color_src / v_color_rest (same shapes as the inputs).
- * tile_counts ((V*T,) int32, zero-filled by the caller, may be NULL) receives the number of
- * intersections of every tile -- the input of the counting sort below. */
+ * tile_counts / tile_keys / tile_capacity (may be NULL / NULL / 0): binning for sb_sort_tiles, see
+ * above. */
 #define SB_FLAG_RAW_SCALES 1
 #define SB_FLAG_RAW_OPACITIES 2
 #define SB_FLAG_COLOR_SIGMOID 4
@@ -207,7 +204,8 @@ SB_API int sb_views_project_fwd(int num_views, int n, const float* means, const 
                          const float* viewmats, int viewmat_stride, const float* intrins, float fx,
                          float fy, float cx, float cy, const float* campos, int img_h, int img_w,
                          int block_width, float clip_thresh, float* packed, float* depths,
-                         int* radii, int* num_tiles_hit, int* tile_counts, sb_stream_t stream);
+                         int* radii, int* num_tiles_hit, int* tile_counts, uint64_t* tile_keys,
+                         int tile_capacity, sb_stream_t stream);
 SB_API int sb_views_project_bwd(int num_views, int n, const float* means, const float* scales,
                          float glob_scale, const float* quats, int sh_degree, int flags,
                          const float* viewmats, int viewmat_stride, const float* intrins, float fx,

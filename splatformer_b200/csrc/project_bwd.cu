@@ -96,13 +96,22 @@ __global__ void __launch_bounds__(kProjBwdBlock) project_bwd_kernel(
 // Fused multi-view backward: counterpart of views_project_fwd_kernel.  Reads the packed gradient
 // record [v_x v_y v_ca v_cb | v_cc v_op v_r v_g | v_b ...] the raster backward accumulated for
 // every (view, Gaussian), recomputes the forward record (this TU is built with --fmad=false like
-// the forward, so `valid` is reproduced exactly), and sums over the views in registers:
+// the forward, so `valid` is reproduced exactly), and sums over the views in registers (four threads
+// per Gaussian take every fourth view each and are joined with two shuffle steps):
 // v_means, v_scales, v_quats, v_opacities and v_coeffs (or v_rgb) are each written once.
 // ------------------------------------------------------------------------------------------------
 constexpr int kViewsBwdBlock = 128;
+constexpr int kViewLanesB = 4;                               // threads sharing one Gaussian (every 4th view each)
+constexpr int kViewsBwdRows = kViewsBwdBlock / kViewLanesB;  // Gaussians per block
+
+__device__ __forceinline__ float sum_view_lanes(float x) {
+  x += __shfl_xor_sync(0xffffffffu, x, 1);
+  x += __shfl_xor_sync(0xffffffffu, x, 2);
+  return x;
+}
 
 template <int DEG>
-__global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
+__global__ void __launch_bounds__(kViewsBwdBlock, 4) views_project_bwd_kernel(
     int num_views, int n, const float* __restrict__ means, const float* __restrict__ scales, float glob,
     const float* __restrict__ quats, int flags, CamSrc cams, const float* __restrict__ campos, int img_h,
     int img_w, int bw, float clip, int k3_store, const float4* __restrict__ packed,
@@ -111,27 +120,30 @@ __global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
     float* __restrict__ v_color_rest) {
   extern __shared__ float smem[];
   constexpr int KU = DEG < 0 ? 1 : (DEG + 1) * (DEG + 1);
-  const int g0 = blockIdx.x * kViewsBwdBlock;
-  const int nb = min(kViewsBwdBlock, n - g0);
-  const int g = g0 + threadIdx.x;
-  const bool active = threadIdx.x < nb;
+  const int g0 = blockIdx.x * kViewsBwdRows;
+  const int nb = min(kViewsBwdRows, n - g0);
+  const int rowi = threadIdx.x / kViewLanesB, sub = threadIdx.x % kViewLanesB;
+  const int g = g0 + rowi;
+  const bool active = rowi < nb;
   float acc[KU * 3];
 #pragma unroll
   for (int i = 0; i < KU * 3; ++i) acc[i] = 0.f;
-  if (active) {
-    const float m[3] = {__ldg(means + 3 * g), __ldg(means + 3 * g + 1), __ldg(means + 3 * g + 2)};
-    float s[3] = {__ldg(scales + 3 * g), __ldg(scales + 3 * g + 1), __ldg(scales + 3 * g + 2)};
+  {
+    // inactive rows (tail block) run on Gaussian n-1 so that the lane-group shuffles stay convergent
+    const int gl = active ? g : n - 1;
+    const float m[3] = {__ldg(means + 3 * gl), __ldg(means + 3 * gl + 1), __ldg(means + 3 * gl + 2)};
+    float s[3] = {__ldg(scales + 3 * gl), __ldg(scales + 3 * gl + 1), __ldg(scales + 3 * gl + 2)};
     if (flags & kFlagRawScales) { s[0] = expf(s[0]); s[1] = expf(s[1]); s[2] = expf(s[2]); }
-    const float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
+    const float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + gl);
     const float q[4] = {q4.x, q4.y, q4.z, q4.w};
     float am[3] = {0, 0, 0}, as[3] = {0, 0, 0}, aq[4] = {0, 0, 0, 0}, aop = 0.f;
     float op = 0.f, col0 = 0.f, col1 = 0.f, col2 = 0.f;
-    for (int v = 0; v < num_views; ++v) {
+    for (int v = sub; v < num_views; v += kViewLanesB) {
       const Cam cam = load_cam(cams, v);
       ProjFwd f;
       project_fwd_one(m, s, glob, q, cam, img_w, img_h, bw, clip, f);
       if (!f.valid) continue;
-      const size_t i = (size_t)v * n + g;
+      const size_t i = (size_t)v * n + gl;
       const float4 ga = __ldg(v_packed + 3 * i), gb = __ldg(v_packed + 3 * i + 1), gc = __ldg(v_packed + 3 * i + 2);
       float vm[3], vs[3], vq[4];
       const float4 col = __ldg(packed + 3 * i + 2);       // r, g, b (after the clamp), opacity
@@ -157,23 +169,40 @@ __global__ void __launch_bounds__(kViewsBwdBlock) views_project_bwd_kernel(
         acc[0] += vr; acc[1] += vg; acc[2] += vb;
       }
     }
+    // join the four view lanes of the Gaussian (op / colour are view-independent: take any lane that saw them)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { am[k] = sum_view_lanes(am[k]); as[k] = sum_view_lanes(as[k]); }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) aq[k] = sum_view_lanes(aq[k]);
+    aop = sum_view_lanes(aop);
+#pragma unroll
+    for (int i = 0; i < KU * 3; ++i) acc[i] = sum_view_lanes(acc[i]);
+    op = fmaxf(fmaxf(op, __shfl_xor_sync(0xffffffffu, op, 1)), fmaxf(__shfl_xor_sync(0xffffffffu, op, 2), __shfl_xor_sync(0xffffffffu, op, 3)));
+    if (DEG < 0 && (flags & kFlagColorSigmoid)) {
+      // colours are in (0, 1) where a view drew the Gaussian and 0 in lanes that saw none
+      col0 = fmaxf(fmaxf(col0, __shfl_xor_sync(0xffffffffu, col0, 1)), fmaxf(__shfl_xor_sync(0xffffffffu, col0, 2), __shfl_xor_sync(0xffffffffu, col0, 3)));
+      col1 = fmaxf(fmaxf(col1, __shfl_xor_sync(0xffffffffu, col1, 1)), fmaxf(__shfl_xor_sync(0xffffffffu, col1, 2), __shfl_xor_sync(0xffffffffu, col1, 3)));
+      col2 = fmaxf(fmaxf(col2, __shfl_xor_sync(0xffffffffu, col2, 1)), fmaxf(__shfl_xor_sync(0xffffffffu, col2, 2), __shfl_xor_sync(0xffffffffu, col2, 3)));
+    }
     // chain rule through the activations the kernel applied itself (gs_utils.py:45,54,65)
     if (flags & kFlagRawScales) { as[0] *= s[0]; as[1] *= s[1]; as[2] *= s[2]; }
     if (flags & kFlagRawOpacities) aop *= op * (1.0f - op);
     if (DEG < 0 && (flags & kFlagColorSigmoid)) {
       acc[0] *= col0 * (1.0f - col0); acc[1] *= col1 * (1.0f - col1); acc[2] *= col2 * (1.0f - col2);
     }
+    if (active && sub == 0) {
 #pragma unroll
-    for (int k = 0; k < 3; ++k) { v_means[3 * g + k] = am[k]; v_scales[3 * g + k] = as[k]; }
-    reinterpret_cast<float4*>(v_quats)[g] = make_float4(aq[0], aq[1], aq[2], aq[3]);
-    v_opacities[g] = aop;
-    if (DEG < 0) { v_color_src[3 * g] = acc[0]; v_color_src[3 * g + 1] = acc[1]; v_color_src[3 * g + 2] = acc[2]; }
+      for (int k = 0; k < 3; ++k) { v_means[3 * g + k] = am[k]; v_scales[3 * g + k] = as[k]; }
+      reinterpret_cast<float4*>(v_quats)[g] = make_float4(aq[0], aq[1], aq[2], aq[3]);
+      v_opacities[g] = aop;
+      if (DEG < 0) { v_color_src[3 * g] = acc[0]; v_color_src[3 * g + 1] = acc[1]; v_color_src[3 * g + 2] = acc[2]; }
+    }
   }
   if (DEG >= 0) {
     const int row = padded_row(k3_store);
-    if (active) {
+    if (active && sub == 0) {
 #pragma unroll
-      for (int i = 0; i < KU * 3; ++i) smem[threadIdx.x * row + i] = acc[i];
+      for (int i = 0; i < KU * 3; ++i) smem[rowi * row + i] = acc[i];
     }
     __syncthreads();
     if (v_color_rest) {
@@ -226,8 +255,8 @@ extern "C" int sb_views_project_bwd(int num_views, int n, const float* means, co
   if (n == 0) return 0;
   sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0};
   const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
-  const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsBwdBlock * (k3 | 1) * sizeof(float);
-  dim3 grid(sb::ceil_div(n, sb::kViewsBwdBlock));
+  const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsBwdRows * (k3 | 1) * sizeof(float);
+  dim3 grid(sb::ceil_div(n, sb::kViewsBwdRows));
   cudaStream_t st = (cudaStream_t)stream;
   const float4* pk = reinterpret_cast<const float4*>(packed);
   const float4* vpk = reinterpret_cast<const float4*>(v_packed);

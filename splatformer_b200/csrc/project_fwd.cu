@@ -43,9 +43,9 @@ __global__ void __launch_bounds__(kProjBlock) project_fwd_kernel(
 // ------------------------------------------------------------------------------------------------
 // Fused multi-view variant (rows a1/a2: the view loop of rasterize_gaussians_to_multiimgs,
 // /root/reference/utils/gs_utils.py:20-27, with the per-view SH colour of :67-79 folded in).
-// One thread per Gaussian keeps its parameters and SH coefficients in registers and walks the V
-// cameras, writing the packed 48-byte raster record, depth, radius and tile count per view.
-// Coefficients are read from HBM once per scene instead of once per view.
+// Four threads per Gaussian keep its parameters and SH coefficients in registers and walk the V
+// cameras (every fourth view each), writing the packed 48-byte raster record, depth, radius and tile
+// count per view.  Coefficients are read from HBM once per scene instead of once per view.
 //   DEG = -1 : color_src is (N,3) view-independent rgb (SplatFormer's degree-0 path, :65)
 //   DEG >= 0 : colour = max(SH(dir) + 0.5, 0)  (:78-79); the coefficients are either one (N,K,3)
 //              array (color_src, color_rest = NULL) or features_dc (N,3) + features_rest (N,K-1,3)
@@ -53,6 +53,8 @@ __global__ void __launch_bounds__(kProjBlock) project_fwd_kernel(
 // `flags` (sb_common.cuh) select raw inputs: log-scales, opacity logits, sigmoid colours, c2w cameras.
 // ------------------------------------------------------------------------------------------------
 constexpr int kViewsBlock = 128;
+constexpr int kViewLanes = 4;                          // threads that share one Gaussian, each taking V/4 views
+constexpr int kViewsRows = kViewsBlock / kViewLanes;   // Gaussians per block
 
 template <int DEG>
 __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
@@ -61,11 +63,13 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     const float* __restrict__ color_src, const float* __restrict__ color_rest, int k3_store, int flags,
     CamSrc cams, const float* __restrict__ campos, int img_h, int img_w, int bw, float clip,
     float4* __restrict__ packed, float* __restrict__ depths, int* __restrict__ radii,
-    int* __restrict__ tiles, int* __restrict__ tile_counts) {
+    int* __restrict__ tiles, int* __restrict__ tile_counts, unsigned long long* __restrict__ tile_keys,
+    int tile_cap) {
   extern __shared__ float smem[];
   constexpr int KU = DEG < 0 ? 1 : (DEG + 1) * (DEG + 1);
-  const int g0 = blockIdx.x * kViewsBlock;
-  const int nb = min(kViewsBlock, n - g0);
+  const int g0 = blockIdx.x * kViewsRows;
+  const int nb = min(kViewsRows, n - g0);
+  const int rowi = threadIdx.x / kViewLanes, sub = threadIdx.x % kViewLanes;
   float c[KU * 3];
   if (DEG >= 0) {
     const int row = padded_row(k3_store);
@@ -77,12 +81,12 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     }
     __syncthreads();
   }
-  const int g = g0 + threadIdx.x;
-  if (threadIdx.x >= nb) return;
+  const int g = g0 + rowi;
+  if (rowi >= nb) return;
   if (DEG >= 0) {
     const int row = padded_row(k3_store);
 #pragma unroll
-    for (int i = 0; i < KU * 3; ++i) c[i] = smem[threadIdx.x * row + i];
+    for (int i = 0; i < KU * 3; ++i) c[i] = smem[rowi * row + i];
   } else {
     c[0] = __ldg(color_src + 3 * g); c[1] = __ldg(color_src + 3 * g + 1); c[2] = __ldg(color_src + 3 * g + 2);
     if (flags & kFlagColorSigmoid) { c[0] = sigmoidf_(c[0]); c[1] = sigmoidf_(c[1]); c[2] = sigmoidf_(c[2]); }
@@ -97,7 +101,7 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
   // blocks start at different views so that, at any moment, the per-tile count reductions of the
   // resident blocks spread over all V*T counters instead of the T counters of one view
   const int v0 = blockIdx.x % num_views;
-  for (int vi = 0; vi < num_views; ++vi) {
+  for (int vi = sub; vi < num_views; vi += kViewLanes) {
     const int v = vi + v0 < num_views ? vi + v0 : vi + v0 - num_views;
     const Cam cam = load_cam(cams, v);
     ProjFwd o;
@@ -107,12 +111,37 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     tiles[i] = o.tiles;
     depths[i] = o.depth;
     if (!o.valid) continue;     // packed record of a culled Gaussian is never read
+    // binning for tile_sort.cu: claim a slot in the fixed-capacity segment of every covered tile and
+    // drop the (depth bits, id) key there.  A tile that runs over keeps counting (the sort kernel
+    // reports the overflow and the host falls back to the global sort).  In the common case (<= 4
+    // tiles) all slots are claimed first and the keys are stored after the colour evaluation, so the
+    // round trips of the atomics overlap each other and the SH arithmetic.
+    size_t tt[4];
+    int pos[4];
+    const unsigned long long key = ((unsigned long long)(unsigned)__float_as_int(o.depth) << 32) | (unsigned)g;
+    const bool few = o.tiles <= 4;
     if (tile_counts) {
-      // per-tile intersection counts for the counting sort of tile_sort.cu
       const int tiles_x = (img_w + bw - 1) / bw;
-      int* tc = tile_counts + (size_t)v * tiles_x * ((img_h + bw - 1) / bw);
-      for (int ty = o.min_y; ty < o.max_y; ++ty)
-        for (int tx = o.min_x; tx < o.max_x; ++tx) atomicAdd(tc + ty * tiles_x + tx, 1);
+      const size_t t0 = (size_t)v * tiles_x * ((img_h + bw - 1) / bw);
+      const int nx = o.max_x - o.min_x;
+      if (few) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (k < o.tiles) {
+            const int ky = (nx == 1) ? k : ((nx >= 4) ? 0 : (nx == 2 ? (k >> 1) : (k == 3)));
+            const int kx = k - ky * nx;
+            tt[k] = t0 + (size_t)(o.min_y + ky) * tiles_x + (o.min_x + kx);
+            pos[k] = atomicAdd(tile_counts + tt[k], 1);
+          }
+        }
+      } else {
+        for (int ty = o.min_y; ty < o.max_y; ++ty)
+          for (int tx = o.min_x; tx < o.max_x; ++tx) {
+            const size_t t = t0 + (size_t)ty * tiles_x + tx;
+            const int p1 = atomicAdd(tile_counts + t, 1);
+            if (p1 < tile_cap) tile_keys[t * tile_cap + p1] = key;
+          }
+      }
     }
     float r, gg, b;
     if (DEG >= 0) {
@@ -128,6 +157,11 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
     }
     float4* p = packed + 3 * i;
     pack_record(o.px, o.py, o.ca, o.cb, o.cc, op, r, gg, b, p[0], p[1], p[2]);
+    if (tile_counts && few) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (k < o.tiles && pos[k] < tile_cap) tile_keys[tt[k] * tile_cap + pos[k]] = key;
+    }
   }
 }
 
@@ -158,24 +192,26 @@ extern "C" int sb_views_project_fwd(int num_views, int n, const float* means, co
                                     const float* intrins, float fx, float fy, float cx, float cy,
                                     const float* campos, int img_h, int img_w, int block_width,
                                     float clip_thresh, float* packed, float* depths, int* radii,
-                                    int* num_tiles_hit, int* tile_counts, sb_stream_t stream) {
+                                    int* num_tiles_hit, int* tile_counts, uint64_t* tile_keys,
+                                    int tile_capacity, sb_stream_t stream) {
   const bool c2w = flags & sb::kFlagC2wOpenGL;
   if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || img_h < 1 || img_w < 1 ||
       sh_degree < -1 || sh_degree > 4 || (sh_degree >= 0 && !campos && !c2w) || (sh_degree < 0 && color_rest) ||
-      ((flags & sb::kFlagColorSigmoid) && sh_degree >= 0))
+      ((flags & sb::kFlagColorSigmoid) && sh_degree >= 0) || (tile_counts && (!tile_keys || tile_capacity < 1)))
     return SB_ERR_BAD_ARG;
   if (n == 0) return 0;
   sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0};
   const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
-  const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsBlock * (k3 | 1) * sizeof(float);
-  dim3 grid(sb::ceil_div(n, sb::kViewsBlock));
+  const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsRows * (k3 | 1) * sizeof(float);
+  dim3 grid(sb::ceil_div(n, sb::kViewsRows));
   cudaStream_t st = (cudaStream_t)stream;
   float4* pk = reinterpret_cast<float4*>(packed);
 #define SB_CASE(D)                                                                                       \
   case D:                                                                                                \
     sb::views_project_fwd_kernel<D><<<grid, sb::kViewsBlock, smem, st>>>(                                \
         num_views, n, means, scales, glob_scale, quats, opacities, color_src, color_rest, k3, flags, cams, \
-        campos, img_h, img_w, block_width, clip_thresh, pk, depths, radii, num_tiles_hit, tile_counts);  \
+        campos, img_h, img_w, block_width, clip_thresh, pk, depths, radii, num_tiles_hit, tile_counts,    \
+        reinterpret_cast<unsigned long long*>(tile_keys), tile_capacity);                                \
     break;
   switch (sh_degree) { SB_CASE(-1) SB_CASE(0) SB_CASE(1) SB_CASE(2) SB_CASE(3) SB_CASE(4) }
 #undef SB_CASE

@@ -16,7 +16,7 @@ namespace sb {
 __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ ids_sorted,
     const int2* __restrict__ tile_bins, const float* __restrict__ background, int tiles_x,
-    int tiles_y, int img_w, int img_h, int bw, const int* __restrict__ view_isect_end,
+    int tiles_y, int img_w, int img_h, int bw, const int* __restrict__ view_has_isects,
     float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx,
     float* __restrict__ out_alpha, int clamp_rgb, const void* __restrict__ gt, int gt_u8,
     float* __restrict__ loss_partial) {
@@ -95,13 +95,9 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
   if (pm.inside) {
     const size_t pix = ((size_t)v * img_h + pm.py_i) * img_w + pm.px_i;
     bool empty_view = false;
-    if (view_isect_end) {
-      // upstream quirk: a view without a single intersection reports final_T = 0
-      // (alpha = 1) while its image is the plain background
-      const int hi = __ldg(view_isect_end + v);
-      const int lo = v ? __ldg(view_isect_end + v - 1) : 0;
-      empty_view = hi - lo < 1;
-    }
+    // upstream quirk: a view without a single intersection reports final_T = 0
+    // (alpha = 1) while its image is the plain background
+    if (view_has_isects) empty_view = __ldg(view_has_isects + v) == 0;
     float r = pr + T * __ldg(background), g = pg + T * __ldg(background + 1), b = pb + T * __ldg(background + 2);
     if (clamp_rgb) { r = fminf(r, 1.0f); g = fminf(g, 1.0f); b = fminf(b, 1.0f); }   // gs_utils.py:111
     final_ts[pix] = empty_view ? 0.f : T;
@@ -141,7 +137,7 @@ __global__ void __launch_bounds__(kRasterBlock) raster_fwd_kernel(
 extern "C" int sb_rasterize_fwd(int num_views, int n, const float* packed,
                                 const int* gaussian_ids_sorted, const int* tile_bins,
                                 const float* background, int img_h, int img_w, int block_width,
-                                const int* view_isect_end, float* out_img, float* final_ts,
+                                const int* view_has_isects, float* out_img, float* final_ts,
                                 int* final_idx, float* out_alpha, int clamp_rgb_max1,
                                 const void* gt, int gt_is_u8, float* loss_partial,
                                 sb_stream_t stream) {
@@ -153,6 +149,6 @@ extern "C" int sb_rasterize_fwd(int num_views, int n, const float* packed,
   sb::raster_fwd_kernel<<<grid, sb::kRasterBlock, 0, (cudaStream_t)stream>>>(
       n, reinterpret_cast<const float4*>(packed), gaussian_ids_sorted,
       reinterpret_cast<const int2*>(tile_bins), background, tiles_x, tiles_y, img_w, img_h, block_width,
-      view_isect_end, out_img, final_ts, final_idx, out_alpha, clamp_rgb_max1, gt, gt_is_u8, loss_partial);
+      view_has_isects, out_img, final_ts, final_idx, out_alpha, clamp_rgb_max1, gt, gt_is_u8, loss_partial);
   SB_RETURN_LAST();
 }

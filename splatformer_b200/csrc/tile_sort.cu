@@ -1,110 +1,24 @@
-// Tile binning for the fused multi-view path: counting sort by tile + per-tile depth sort.
+// Tile binning for the fused multi-view path: fixed-capacity tile segments + per-tile depth sort.
 //
-// Replaces, for scenes whose tiles hold at most kMaxSegment Gaussians, the chain
-//   cumsum -> map_gaussian_to_intersects -> 64-bit radix sort -> get_tile_bin_edges
+// Replaces, for scenes whose tiles hold at most `cap` Gaussians, the chain
+//   cumsum -> .item() -> map_gaussian_to_intersects -> 64-bit radix sort -> get_tile_bin_edges
 // (upstream gsplat.utils.bin_and_sort_gaussians reached from
 // gsplat.rasterize_gaussians, /root/reference/utils/gs_utils.py:96-109) with
-//   1. per-tile intersection counts, accumulated with global reductions by the projection kernel,
-//   2. one exclusive scan over the V*T counts  -> tile_bins (start, end) directly,
-//   3. a scatter of (depth bits << 32 | gaussian id) into the tile's segment (atomic cursor),
-//   4. a bitonic sort of every segment in shared memory, keyed on (depth, id).
-// The result is the same gaussian_ids_sorted / tile_bins the global sort produces: within a tile the
-// stable radix sort orders by depth bits and, for equal depths, by emission order, which is
-// ascending Gaussian id -- exactly the (depth, id) order used here.  Traffic: 12 bytes written + 8
-// read + 4 written per intersection instead of six radix passes over 12-byte pairs.
+//   1. the projection kernel dropping (depth bits << 32 | gaussian id) straight into the segment
+//      [tile * cap, tile * cap + count) of every tile a Gaussian covers (one atomic slot claim each),
+//   2. one kernel that sorts every segment in shared memory on (depth, id) and writes
+//      gaussian_ids_sorted, tile_bins, the per-view "has intersections" flags and the totals.
+// Within a tile the result is exactly what the stable global sort produces: ascending depth bits,
+// ties in emission order = ascending Gaussian id.  Nothing on the host has to know the number of
+// intersections, so the forward pass needs no synchronisation before the raster kernel.
+// Traffic: 8 bytes written + 8 read + 4 written per intersection instead of a scan, a 12-byte
+// emission and six radix passes over 12-byte pairs.
 #include "sb_common.cuh"
 
 namespace sb {
 
-constexpr int kMaxSegment = 8192;     // Gaussians per tile the shared-memory sort can take (96 KB)
-constexpr int kScanBlock = 1024;
+constexpr int kMaxSegment = 8192;     // largest tile capacity the shared-memory sort takes (96 KB)
 constexpr int kSortBlock = 256;
-
-// Single-CTA exclusive scan of the tile counts.  totals[0] = number of intersections, totals[1] =
-// largest tile count.
-// view_end[v] = intersections of views 0..v (what the raster kernel uses to spot a view without any).
-__global__ void __launch_bounds__(kScanBlock) tile_offsets_kernel(int num_tiles, int tiles_per_view,
-                                                                  const int* __restrict__ counts,
-                                                                  int2* __restrict__ bins, int* __restrict__ totals,
-                                                                  int* __restrict__ view_end) {
-  __shared__ int s_warp[kScanBlock / 32];
-  __shared__ int s_carry;
-  __shared__ int s_max[kScanBlock / 32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) s_carry = 0;
-  int vmax = 0;
-  __syncthreads();
-  for (int base = 0; base < num_tiles; base += kScanBlock) {
-    const int i = base + threadIdx.x;
-    const int c = i < num_tiles ? __ldg(counts + i) : 0;
-    vmax = max(vmax, c);
-    int x = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
-    }
-    if (lane == 31) s_warp[warp] = x;
-    __syncthreads();
-    if (warp == 0) {
-      int w = s_warp[lane];
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int y = __shfl_up_sync(0xffffffffu, w, o);
-        if (lane >= o) w += y;
-      }
-      s_warp[lane] = w;
-    }
-    __syncthreads();
-    const int carry = s_carry;
-    const int incl = carry + (warp ? s_warp[warp - 1] : 0) + x;
-    // empty tiles keep (0, 0) like upstream's zero-initialised tile_bins
-    if (i < num_tiles) {
-      bins[i] = c > 0 ? make_int2(incl - c, incl) : make_int2(0, 0);
-      if ((i + 1) % tiles_per_view == 0) view_end[i / tiles_per_view] = incl;
-    }
-    __syncthreads();
-    if (threadIdx.x == kScanBlock - 1) s_carry = incl;
-    __syncthreads();
-  }
-  vmax = __reduce_max_sync(0xffffffffu, vmax);
-  if (lane == 0) s_max[warp] = vmax;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int m = 0;
-    for (int w = 0; w < kScanBlock / 32; ++w) m = max(m, s_max[w]);
-    totals[0] = s_carry;
-    totals[1] = m;
-  }
-}
-
-// One thread per (view, Gaussian): claims a slot in every tile of its bbox.  `cursors` holds the tile
-// counts on entry and is counted down to zero (slot = start + old - 1), so no second zero-fill is needed.
-// Consecutive blocks take consecutive VIEWS of the same Gaussian chunk: the resident blocks then hit
-// the counters of all views at once (contention per counter drops by V) while loads stay coalesced.
-__global__ void __launch_bounds__(256) scatter_isects_kernel(
-    int num_views, int n, const float* __restrict__ xys, int xy_stride, const float* __restrict__ depths,
-    const int* __restrict__ radii, int tiles_x, int tiles_y, int bw, const int2* __restrict__ bins,
-    int* __restrict__ cursors, unsigned long long* __restrict__ keys) {
-  const int v = blockIdx.x % num_views;
-  const int g = (blockIdx.x / num_views) * 256 + threadIdx.x;
-  if (g >= n) return;
-  const size_t i = (size_t)v * n + g;
-  const int r = __ldg(radii + i);
-  if (r <= 0) return;
-  const float2 c = __ldg(reinterpret_cast<const float2*>(xys + i * xy_stride));
-  int min_x, max_x, min_y, max_y;
-  tile_bbox(c.x, c.y, (float)r, tiles_x, tiles_y, bw, min_x, max_x, min_y, max_y);
-  const unsigned long long key =
-      ((unsigned long long)(unsigned)__float_as_int(__ldg(depths + i)) << 32) | (unsigned)g;
-  const int tile0 = v * tiles_x * tiles_y;
-  for (int ty = min_y; ty < max_y; ++ty)
-    for (int tx = min_x; tx < max_x; ++tx) {
-      const int t = tile0 + ty * tiles_x + tx;
-      const int old = atomicSub(cursors + t, 1);
-      keys[(size_t)__ldg(&bins[t].x) + (old - 1)] = key;
-    }
-}
 
 // ------------------------------------------------------------------------------------------------
 // Per-tile sort of the (depth bits << 32 | id) keys, one CTA per tile, in shared memory.
@@ -133,17 +47,27 @@ __device__ __forceinline__ void bitonic_sort_smem(unsigned long long* s, int len
   }
 }
 
-// dynamic shared memory: keys[cap] (8 B each) then ends[cap] (4 B each), cap = power of two >= max tile count
-__global__ void __launch_bounds__(kSortBlock) sort_tiles_kernel(int cap, const int2* __restrict__ bins,
+// dynamic shared memory: keys[cap] (8 B each) then ends[cap] (4 B each); cap = segment capacity (power of two)
+// totals: [0] += intersections, [1] = 1 if some tile overflowed its segment.
+__global__ void __launch_bounds__(kSortBlock) sort_tiles_kernel(int cap, int tiles_per_view,
+                                                                const int* __restrict__ counts,
                                                                 const unsigned long long* __restrict__ keys,
-                                                                int* __restrict__ gids_sorted) {
+                                                                int* __restrict__ gids_sorted, int2* __restrict__ bins,
+                                                                int* __restrict__ view_has, int* __restrict__ totals) {
   extern __shared__ unsigned long long s_keys[];
   int* s_end = reinterpret_cast<int*>(s_keys + cap);
   __shared__ unsigned s_min, s_max;
   __shared__ int s_warp[kSortBlock / 32], s_carry, s_overflow;
-  const int2 range = __ldg(bins + blockIdx.x);
-  const int len = range.y - range.x;
-  if (len <= 0 || len > cap) return;      // (len > cap: the host never launches this path for such scenes)
+  const int count = __ldg(counts + blockIdx.x);
+  const int len = min(count, cap);
+  const int2 range = make_int2(blockIdx.x * cap, blockIdx.x * cap + len);       // V*T*cap < 2^31 (host checks)
+  if (threadIdx.x == 0) {
+    // empty tiles keep (0, 0) like upstream's zero-initialised tile_bins
+    bins[blockIdx.x] = len > 0 ? range : make_int2(0, 0);
+    if (len > 0) { view_has[blockIdx.x / tiles_per_view] = 1; atomicAdd(totals, len); }
+    if (count > cap) totals[1] = 1;
+  }
+  if (len <= 0) return;
   const unsigned long long* src = keys + range.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (len <= 32) {
@@ -235,40 +159,18 @@ __global__ void __launch_bounds__(kSortBlock) sort_tiles_kernel(int cap, const i
 
 extern "C" int sb_tile_sort_capacity(void) { return sb::kMaxSegment; }
 
-extern "C" int sb_tile_offsets(int num_views, int tiles_per_view, const int* tile_counts, int* tile_bins,
-                               int* totals, int* view_isect_end, sb_stream_t stream) {
-  if (num_views < 1 || tiles_per_view < 1 || !tile_counts || !tile_bins || !totals || !view_isect_end)
+extern "C" int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, const int* tile_counts,
+                             const uint64_t* tile_keys, int* gaussian_ids_sorted, int* tile_bins,
+                             int* view_has_isects, int* totals, sb_stream_t stream) {
+  if (num_views < 1 || tiles_per_view < 1 || tile_capacity < 64 || tile_capacity > sb::kMaxSegment ||
+      (tile_capacity & (tile_capacity - 1)) ||
+      (long long)num_views * tiles_per_view * tile_capacity > 2147483647LL)
     return SB_ERR_BAD_ARG;
-  sb::tile_offsets_kernel<<<1, sb::kScanBlock, 0, (cudaStream_t)stream>>>(
-      num_views * tiles_per_view, tiles_per_view, tile_counts, reinterpret_cast<int2*>(tile_bins), totals,
-      view_isect_end);
-  SB_RETURN_LAST();
-}
-
-extern "C" int sb_scatter_isects(int num_views, int n, const float* xys, int xys_stride, const float* depths,
-                                 const int* radii, int tiles_x, int tiles_y, int block_width,
-                                 const int* tile_bins, int* tile_counts, uint64_t* isect_keys,
-                                 sb_stream_t stream) {
-  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || xys_stride < 2 || (xys_stride & 1))
-    return SB_ERR_BAD_ARG;
-  if (n == 0) return 0;
-  sb::scatter_isects_kernel<<<(unsigned)num_views * (unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      num_views, n, xys, xys_stride, depths, radii, tiles_x, tiles_y, block_width,
-      reinterpret_cast<const int2*>(tile_bins), tile_counts, reinterpret_cast<unsigned long long*>(isect_keys));
-  SB_RETURN_LAST();
-}
-
-extern "C" int sb_sort_tiles(int num_tiles_total, int max_tile_count, const int* tile_bins,
-                             const uint64_t* isect_keys, int* gaussian_ids_sorted, sb_stream_t stream) {
-  if (num_tiles_total < 1 || max_tile_count > sb::kMaxSegment) return SB_ERR_BAD_ARG;
-  if (max_tile_count <= 0) return 0;
-  int cap = 64;
-  while (cap < max_tile_count) cap <<= 1;
-  const size_t smem = (size_t)cap * 12;
-  if (smem > 48 * 1024)
+  const size_t smem = (size_t)tile_capacity * 12;
+  if (smem > 40 * 1024)      // the kernel also has a little static shared memory
     cudaFuncSetAttribute(sb::sort_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  sb::sort_tiles_kernel<<<num_tiles_total, sb::kSortBlock, smem, (cudaStream_t)stream>>>(
-      cap, reinterpret_cast<const int2*>(tile_bins), reinterpret_cast<const unsigned long long*>(isect_keys),
-      gaussian_ids_sorted);
+  sb::sort_tiles_kernel<<<num_views * tiles_per_view, sb::kSortBlock, smem, (cudaStream_t)stream>>>(
+      tile_capacity, tiles_per_view, tile_counts, reinterpret_cast<const unsigned long long*>(tile_keys),
+      gaussian_ids_sorted, reinterpret_cast<int2*>(tile_bins), view_has_isects, totals);
   SB_RETURN_LAST();
 }

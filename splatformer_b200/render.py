@@ -81,6 +81,30 @@ def _c(t: Tensor) -> Tensor:
 
 
 _side_streams: Dict[int, torch.cuda.Stream] = {}
+_pinned: Dict[int, Tensor] = {}
+_overflowed: Dict[Tuple[int, int, int], int] = {}
+DEFAULT_TILE_CAPACITY = 2048        # doubled per overflow of a (views, tiles, Gaussians) shape, up to the library's limit
+
+
+def _pinned_pair(device) -> Tensor:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _pinned:
+        _pinned[idx] = torch.zeros(2, dtype=I32).pin_memory()
+    return _pinned[idx]
+
+
+def _tile_capacity(lib, v: int, num_tiles: int, n: int) -> int:
+    """Segment capacity for the tile sort, or 0 to use the global sort.  A (views, tiles, Gaussians)
+    shape whose tiles overflowed the capacity gets twice the capacity next time; past the library's
+    limit it goes straight to the global sort."""
+    cap = DEFAULT_TILE_CAPACITY << _overflowed.get((v, num_tiles, n), 0)
+    if cap > lib.sb_tile_sort_capacity() or v * num_tiles * cap >= 2 ** 31:
+        return 0
+    return cap
+
+
+def _note_overflow(v: int, num_tiles: int, n: int) -> None:
+    _overflowed[(v, num_tiles, n)] = _overflowed.get((v, num_tiles, n), 0) + 1
 
 
 def _side_stream(device) -> torch.cuda.Stream:
@@ -138,54 +162,74 @@ class _RenderViews(Function):
         radii = torch.empty(v, n, dtype=I32, device=dev)
         tiles_hit = torch.empty(v, n, dtype=I32, device=dev)
         num_tiles = tiles_x * tiles_y
-        with _stage("zero_counts"):
-            tile_counts = torch.zeros(v * num_tiles, dtype=I32, device=dev)
-        with _stage("project_sh_fwd"):
-            _abi.check(lib.sb_views_project_fwd(
-                v, n, _abi.ptr(means, F32, "means"), _abi.ptr(scales, F32, "scales"), 1.0,
-                _abi.ptr(quats, F32, "quats"), _abi.ptr(opacities, F32, "opacities"),
-                _abi.ptr(color_src, F32, "color_src"), _abi.ptr(color_rest, F32, "color_rest"), sh_degree, flags,
-                _abi.ptr(viewmats, F32, "viewmats"), vm_stride, _abi.ptr(intrins, F32, "intrins"), 0.0, 0.0, 0.0,
-                0.0, _abi.ptr(campos, F32, "campos"), img_height, img_width, block_width, clip_thresh,
-                _abi.ptr(packed, F32, "packed"), _abi.ptr(depths, F32, "depths"),
-                _abi.ptr(radii, I32, "radii"), _abi.ptr(tiles_hit, I32, "num_tiles_hit"),
-                _abi.ptr(tile_counts, I32, "tile_counts"), _abi.stream()), "sb_views_project_fwd")
-        tile_bins = torch.empty(v * num_tiles, 2, dtype=I32, device=dev)
-        view_end = torch.empty(v, dtype=I32, device=dev)
-        totals = torch.empty(2, dtype=I32, device=dev)
-        with _stage("tile_offsets"):
-            _abi.check(lib.sb_tile_offsets(v, num_tiles, _abi.ptr(tile_counts, I32, "tile_counts"),
-                                           _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(totals, I32, "totals"),
-                                           _abi.ptr(view_end, I32, "view_isect_end"), _abi.stream()),
-                       "sb_tile_offsets")
-            # the one host synchronisation of the scene: sizes the intersection buffers
-            num_intersects, max_tile_count = (int(x) for x in totals.tolist())
-        global _last_num_intersects
-        _last_num_intersects = num_intersects
         out_img = torch.empty(v, img_height, img_width, 3, dtype=F32, device=dev)
         final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
         final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)
         out_alpha = None if gt is not None else torch.empty(v, img_height, img_width, dtype=F32, device=dev)
         loss_partial = None if gt is None else torch.empty(v, num_tiles, 2, dtype=F32, device=dev)
-        if max_tile_count <= lib.sb_tile_sort_capacity():
-            # counting sort by tile + per-tile (depth, id) sort in shared memory (csrc/tile_sort.cu)
-            keys = torch.empty(max(num_intersects, 1), dtype=torch.int64, device=dev)
-            gids_sorted = torch.empty(max(num_intersects, 1), dtype=I32, device=dev)
-            with _stage("scatter_isects"):
-                _abi.check(lib.sb_scatter_isects(
-                    v, n, _abi.ptr(packed, F32, "packed"), 12, _abi.ptr(depths, F32, "depths"),
-                    _abi.ptr(radii, I32, "radii"), tiles_x, tiles_y, block_width,
-                    _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(tile_counts, I32, "tile_counts"),
-                    _abi.ptr(keys, torch.int64, "isect_keys"), _abi.stream()), "sb_scatter_isects")
+
+        def project(tile_counts, tile_keys, cap):
+            with _stage("project_sh_fwd"):
+                _abi.check(lib.sb_views_project_fwd(
+                    v, n, _abi.ptr(means, F32, "means"), _abi.ptr(scales, F32, "scales"), 1.0,
+                    _abi.ptr(quats, F32, "quats"), _abi.ptr(opacities, F32, "opacities"),
+                    _abi.ptr(color_src, F32, "color_src"), _abi.ptr(color_rest, F32, "color_rest"), sh_degree,
+                    flags, _abi.ptr(viewmats, F32, "viewmats"), vm_stride, _abi.ptr(intrins, F32, "intrins"), 0.0,
+                    0.0, 0.0, 0.0, _abi.ptr(campos, F32, "campos"), img_height, img_width, block_width,
+                    clip_thresh, _abi.ptr(packed, F32, "packed"), _abi.ptr(depths, F32, "depths"),
+                    _abi.ptr(radii, I32, "radii"), _abi.ptr(tiles_hit, I32, "num_tiles_hit"),
+                    _abi.ptr(tile_counts, I32, "tile_counts"), _abi.ptr(tile_keys, torch.int64, "tile_keys"), cap,
+                    _abi.stream()), "sb_views_project_fwd")
+
+        def raster(gids_sorted, tile_bins, view_has):
+            if gt_ready is not None:
+                torch.cuda.current_stream().wait_event(gt_ready)
+            with _stage("raster_fwd"):
+                _abi.check(lib.sb_rasterize_fwd(
+                    v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
+                    _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
+                    img_width, block_width, _abi.ptr(view_has, I32, "view_has_isects"),
+                    _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
+                    _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
+                    1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,
+                    _abi.ptr(loss_partial, F32, "loss_partial"), _abi.stream()), "sb_rasterize_fwd")
+
+        global _last_num_intersects
+        cap = _tile_capacity(lib, v, num_tiles, n)
+        done = False
+        if cap:
+            # fixed-capacity tile segments + per-tile sort (csrc/tile_sort.cu).  The raster kernel is
+            # enqueued optimistically; the host then reads the overflow flag, which the GPU produced
+            # BEFORE the raster kernel started -- the device never idles on this round trip.
+            with _stage("zero_counts"):
+                state = torch.zeros(v * num_tiles + v + 2, dtype=I32, device=dev)
+            tile_counts, view_has, totals = state[:v * num_tiles], state[v * num_tiles:-2], state[-2:]
+            tile_keys = torch.empty(v * num_tiles * cap, dtype=torch.int64, device=dev)
+            gids_sorted = torch.empty(v * num_tiles * cap, dtype=I32, device=dev)
+            tile_bins = torch.empty(v * num_tiles, 2, dtype=I32, device=dev)
+            project(tile_counts, tile_keys, cap)
             with _stage("sort_tiles"):
-                _abi.check(lib.sb_sort_tiles(v * num_tiles, max_tile_count, _abi.ptr(tile_bins, I32, "tile_bins"),
-                                             _abi.ptr(keys, torch.int64, "isect_keys"),
-                                             _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"), _abi.stream()),
-                           "sb_sort_tiles")
-        else:
+                _abi.check(lib.sb_sort_tiles(
+                    v, num_tiles, cap, _abi.ptr(tile_counts, I32, "tile_counts"),
+                    _abi.ptr(tile_keys, torch.int64, "tile_keys"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
+                    _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(view_has, I32, "view_has_isects"),
+                    _abi.ptr(totals, I32, "totals"), _abi.stream()), "sb_sort_tiles")
+            host_totals = _pinned_pair(dev)
+            host_totals.copy_(totals, non_blocking=True)
+            flag_ready = torch.cuda.Event()
+            flag_ready.record()
+            raster(gids_sorted, tile_bins, view_has)
+            flag_ready.synchronize()
+            num_intersects, overflow = int(host_totals[0]), int(host_totals[1])
+            done = overflow == 0
+            if not done:
+                _note_overflow(v, num_tiles, n)
+        if not done:
             # very deep tiles: global 64-bit (tile | depth) radix sort, as the per-view API does
+            if not cap:
+                project(None, None, 0)
             with _stage("cumsum"):
-                _, cum = utils.compute_cumulative_intersects(tiles_hit, sync=False)
+                num_intersects, cum = utils.compute_cumulative_intersects(tiles_hit)
             with _stage("map_isect"):
                 isect_ids, gaussian_ids = _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x,
                                                tiles_y, block_width)
@@ -193,17 +237,10 @@ class _RenderViews(Function):
                 isect_sorted, gids_sorted = utils.sort_isects(isect_ids, gaussian_ids, num_tiles * v)
             with _stage("bin_edges"):
                 tile_bins = utils.get_tile_bin_edges(num_intersects, isect_sorted, (tiles_x, tiles_y, 1), v)
-        if gt_ready is not None:
-            torch.cuda.current_stream().wait_event(gt_ready)
-        with _stage("raster_fwd"):
-            _abi.check(lib.sb_rasterize_fwd(
-                v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
-                _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
-                img_width, block_width, _abi.ptr(view_end, I32, "view_isect_end"), _abi.ptr(out_img, F32, "out_img"),
-                _abi.ptr(final_ts, F32, "final_Ts"),
-                _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
-                1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,
-                _abi.ptr(loss_partial, F32, "loss_partial"), _abi.stream()), "sb_rasterize_fwd")
+            ends = cum.view(v, n)[:, -1]
+            view_has = (torch.diff(ends, prepend=ends.new_zeros(1)) > 0).to(I32)
+            raster(gids_sorted, tile_bins, view_has)
+        _last_num_intersects = num_intersects
         ctx.meta = (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride,
                     tuple(color_src.shape), None if color_rest is None else tuple(color_rest.shape),
                     num_intersects, clamp_rgb)

@@ -25,7 +25,7 @@ def test_header_declares_the_expected_entry_points():
     d = _declared()
     for name in ("sb_sh_fwd", "sb_sh_bwd", "sb_project_fwd", "sb_project_bwd", "sb_cumsum_i32",
                  "sb_map_gaussian_to_intersects", "sb_sort_pairs", "sb_tile_bin_edges", "sb_rasterize_fwd",
-                 "sb_rasterize_bwd", "sb_views_project_fwd", "sb_views_project_bwd"):
+                 "sb_rasterize_bwd", "sb_views_project_fwd", "sb_views_project_bwd", "sb_sort_tiles"):
         assert name in d, name
 
 
@@ -52,7 +52,9 @@ def test_no_torch_types_or_cpu_fallback_in_the_boundary():
     from splatformer_b200 import _abi
     lib = _abi.load()
     assert lib.sb_sort_pairs(-1, 40, None, None, None, None, None, 0, None) == -1
-    assert lib.sb_rasterize_fwd(1, 0, None, None, None, None, 16, 16, 17, None, None, None, None, None, 0, None) == -1
+    assert lib.sb_rasterize_fwd(1, 0, None, None, None, None, 16, 16, 17, None, None, None, None, None, 0, None, 0,
+                                None, None) == -1           # block_width 17
+    assert lib.sb_sort_tiles(1, 64, 100, None, None, None, None, None, None, None) == -1    # capacity not a power of two
     assert lib.sb_sh_fwd(1, 4, 2, 3, None, None, None, None) == -1      # degrees_to_use > degree
 
 

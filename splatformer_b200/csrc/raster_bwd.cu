@@ -20,9 +20,12 @@ namespace sb {
 
 constexpr int kSlots = 16;          // hits parked per warp before a flush
 constexpr int kSlotStride = 33;     // float2 units; odd stride keeps the transposed LDS.64 conflict-free
-constexpr int kWarps = kRasterBlock / 32;
-constexpr size_t kBwdSmem = sizeof(float4) * (3 * kBatch + kWarps * 32) + sizeof(float2) * kWarps * kSlots * kSlotStride
-                            + sizeof(int) * kBatch;
+// NW warps per CTA: 8 = one CTA per tile; 4 = two CTAs per 16x16 tile (upper / lower half), which halves
+// the number of warps that wait for each other at the staging barrier.  Each CTA stages NW*32 Gaussians
+// per batch.
+constexpr size_t bwd_smem(int nw) {
+  return sizeof(float4) * (3 * nw * 32 + nw * 32) + sizeof(float2) * nw * kSlots * kSlotStride + sizeof(int) * nw * 32;
+}
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -91,8 +94,8 @@ __device__ __forceinline__ void flush_slots(const float2* __restrict__ myW, cons
   __syncwarp();
 }
 
-template <bool RECT>
-__global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
+template <bool RECT, int NW>
+__global__ void __launch_bounds__(NW * 32) raster_bwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ ids_sorted,
     const int2* __restrict__ tile_bins, const float* __restrict__ background, int tiles_x,
     int tiles_y, int img_w, int img_h, int bw, int clamped, const float* __restrict__ final_ts,
@@ -100,17 +103,20 @@ __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
     const float* __restrict__ v_out_alpha, const float* __restrict__ out_img_clamped,
     const void* __restrict__ gt, int gt_u8, const float* __restrict__ v_loss, float* __restrict__ v_packed) {
   extern __shared__ float4 smem4[];
+  constexpr int kB = NW * 32;      // Gaussians staged per batch
+  constexpr int kParts = 8 / NW;   // CTAs per tile
   float4* sA = smem4;
-  float4* sB = sA + kBatch;
-  float4* sC = sB + kBatch;
-  float4* sVo = sC + kBatch;                                       // [kWarps][32]  v_out rgb per pixel
-  float2* sW = reinterpret_cast<float2*>(sVo + kWarps * 32);       // [kWarps][kSlots][kSlotStride]
-  int* sG = reinterpret_cast<int*>(sW + kWarps * kSlots * kSlotStride);
-  const int tile = blockIdx.x, v = blockIdx.y;
+  float4* sB = sA + kB;
+  float4* sC = sB + kB;
+  float4* sVo = sC + kB;                                       // [NW][32]  v_out rgb per pixel
+  float2* sW = reinterpret_cast<float2*>(sVo + NW * 32);       // [NW][kSlots][kSlotStride]
+  int* sG = reinterpret_cast<int*>(sW + NW * kSlots * kSlotStride);
+  const int tile = blockIdx.x / kParts, part = blockIdx.x % kParts, v = blockIdx.y;
   const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
-  const PixelMap pm = make_pixel_map(tile_x, tile_y, bw, img_w, img_h);
+  const PixelMap pm = make_pixel_map(tile_x, tile_y, bw, img_w, img_h, part * NW);
   const float px = (float)pm.px_i + 0.5f, py = (float)pm.py_i + 0.5f;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warp_t = warp + part * NW;                          // warp index within the tile
   const int2 range = __ldg(tile_bins + (size_t)v * tiles_x * tiles_y + tile);
   const int count = range.y - range.x;
   if (count <= 0) return;
@@ -150,11 +156,11 @@ __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
   float4* myVo = sVo + warp * 32;
   float2* myW = sW + warp * kSlots * kSlotStride;
   myVo[lane] = make_float4(vo_r, vo_g, vo_b, 0.f);
-  __shared__ float2 sP[RECT ? 1 : kWarps * 32];      // per-lane pixel centres (block widths other than 16)
+  __shared__ float2 sP[RECT ? 1 : NW * 32];          // per-lane pixel centres (block widths other than 16)
   const float2* myP = sP;
   if (!RECT) { sP[warp * 32 + lane] = make_float2(px, py); myP = sP + warp * 32; }
-  const float ox = (float)(tile_x * bw + (warp & 1) * 8) + 0.5f;
-  const float oy = (float)(tile_y * bw + (warp >> 1) * 4) + 0.5f;
+  const float ox = (float)(tile_x * bw + (warp_t & 1) * 8) + 0.5f;
+  const float oy = (float)(tile_y * bw + (warp_t >> 1) * 4) + 0.5f;
   const float bg_dot = __ldg(background) * vo_r + __ldg(background + 1) * vo_g + __ldg(background + 2) * vo_b;
   const int warp_final = __reduce_max_sync(0xffffffffu, bin_final);
   // v_alpha = T * (rgb . v_out) - ra * acc,  acc = sum_{behind} fac_j (rgb_j . v_out) - T_final (v_out_alpha - bg . v_out)
@@ -164,9 +170,9 @@ __global__ void __launch_bounds__(kRasterBlock) raster_bwd_kernel(
   float own_x = 0.f, own_y = 0.f;
   int own_g = 0;
 
-  for (int b0 = 0; b0 < count; b0 += kBatch) {
+  for (int b0 = 0; b0 < count; b0 += kB) {
     __syncthreads();
-    const int bsize = min(kBatch, count - b0);
+    const int bsize = min(kB, count - b0);
     if (threadIdx.x < bsize) {
       const int g = __ldg(ids_sorted + range.y - 1 - b0 - threadIdx.x);   // slot s <-> idx = end-1-b0-s
       const float4* p = vp + (size_t)g * 3;
@@ -228,16 +234,16 @@ extern "C" int sb_rasterize_bwd(int num_views, int n, const float* packed,
       (!v_out_img && !gt && !v_out_alpha) || (gt && (!out_img || !v_loss)) || (clamped_rgb_max1 && !out_img))
     return SB_ERR_BAD_ARG;
   const int tiles_x = sb::ceil_div(img_w, block_width), tiles_y = sb::ceil_div(img_h, block_width);
-  dim3 grid(tiles_x * tiles_y, num_views);
   // opting in to > 48 KB of dynamic shared memory is idempotent per-function state, not library state
-  cudaFuncSetAttribute(sb::raster_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb::kBwdSmem);
-  cudaFuncSetAttribute(sb::raster_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb::kBwdSmem);
-#define SB_LAUNCH(RECT)                                                                                   \
-  sb::raster_bwd_kernel<RECT><<<grid, sb::kRasterBlock, sb::kBwdSmem, (cudaStream_t)stream>>>(            \
+  cudaFuncSetAttribute(sb::raster_bwd_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       (int)sb::bwd_smem(8));
+#define SB_LAUNCH(RECT, NW)                                                                               \
+  sb::raster_bwd_kernel<RECT, NW><<<dim3(tiles_x * tiles_y * (8 / NW), num_views), NW * 32, sb::bwd_smem(NW), \
+                                    (cudaStream_t)stream>>>(                                              \
       n, reinterpret_cast<const float4*>(packed), gaussian_ids_sorted,                                    \
       reinterpret_cast<const int2*>(tile_bins), background, tiles_x, tiles_y, img_w, img_h, block_width,  \
       clamped_rgb_max1, final_ts, final_idx, v_out_img, v_out_alpha, out_img, gt, gt_is_u8, v_loss, v_packed)
-  if (block_width == 16) SB_LAUNCH(true); else SB_LAUNCH(false);
+  if (block_width == 16) SB_LAUNCH(true, 4); else SB_LAUNCH(false, 8);
 #undef SB_LAUNCH
   SB_RETURN_LAST();
 }

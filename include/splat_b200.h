@@ -168,7 +168,30 @@ SB_API int sb_unpack_splat_grads(int count, const float* v_packed, const float* 
 SB_API int sb_tile_sort_capacity(void);
 SB_API int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, const int* tile_counts,
                   const uint64_t* tile_keys, int* gaussian_ids_sorted, int* tile_bins,
-                  int* view_has_isects, int* totals, sb_stream_t stream);
+                  int* view_has_isects, int* totals, int n, int tiles_x, const float* packed,
+                  int* rect_ids, int* rect_counts, sb_stream_t stream);
+
+/* ---- a10 / a11 for the fused path: rect-list rasteriser (block width 16 only) -------------
+ * A 16x16 tile is eight 8x4-pixel rectangles (rect r: columns 8*(r&1).., rows 4*(r>>1)..).  Given
+ * rect_ids (V*T*8*capacity) and rect_counts (V*T*8), sb_sort_tiles additionally writes, for every
+ * rectangle, the depth-ordered ids of the Gaussians whose {alpha >= 1/255} region reaches it (exact
+ * ellipse / rectangle test, conservatively inflated) into rect_ids[(tile*8 + r)*capacity + ...]
+ * (gaussian_ids_sorted may then be NULL).  The two kernels below give each rectangle to one warp,
+ * which walks its own list with no block-level synchronisation: same compositing order, same images
+ * and gradients as sb_rasterize_fwd / _bwd (the dropped pairs are ones those kernels skip).
+ * final_idx here is the position in the rectangle's list of the last composited Gaussian (-1: none);
+ * it is only meaningful to sb_rasterize_rect_bwd.  All other arguments as sb_rasterize_fwd / _bwd. */
+SB_API int sb_rasterize_rect_fwd(int num_views, int n, const float* packed, const int* rect_ids,
+                          const int* rect_counts, int rect_capacity, const float* background,
+                          int img_h, int img_w, const int* view_has_isects, float* out_img,
+                          float* final_ts, int* final_idx, float* out_alpha, int clamp_rgb_max1,
+                          const void* gt, int gt_is_u8, float* loss_partial, sb_stream_t stream);
+SB_API int sb_rasterize_rect_bwd(int num_views, int n, const float* packed, const int* rect_ids,
+                          const int* rect_counts, int rect_capacity, const float* background,
+                          int img_h, int img_w, const float* final_ts, const int* final_idx,
+                          const float* v_out_img, const float* v_out_alpha, const float* out_img,
+                          int clamped_rgb_max1, const void* gt, int gt_is_u8, const float* v_loss,
+                          float* v_packed, sb_stream_t stream);
 
 /* ---- a1 / a2: fused multi-view projection + SH colour ----------------------------------
  * The view loop of rasterize_gaussians_to_multiimgs (gs_utils.py:20-27) with the per-view

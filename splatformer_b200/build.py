@@ -36,6 +36,7 @@ UNITS = {
     "tile_sort.cu": [],
     "raster_fwd.cu": [],
     "raster_bwd.cu": [],
+    "raster_rect.cu": [],
 }
 
 

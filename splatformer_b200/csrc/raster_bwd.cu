@@ -18,8 +18,6 @@
 
 namespace sb {
 
-constexpr int kSlots = 16;          // hits parked per warp before a flush
-constexpr int kSlotStride = 33;     // float2 units; odd stride keeps the transposed LDS.64 conflict-free
 // NW warps per CTA: 8 = one CTA per tile; 4 = two CTAs per 16x16 tile (upper / lower half), which halves
 // the number of warps that wait for each other at the staging barrier.  Each CTA stages NW*32 Gaussians
 // per batch.
@@ -27,72 +25,6 @@ constexpr size_t bwd_smem(int nw) {
   return sizeof(float4) * (3 * nw * 32 + nw * 32) + sizeof(float2) * nw * kSlots * kSlotStride + sizeof(int) * nw * 32;
 }
 
-__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
-}
-
-// Sums the parked hits of this warp and issues the global reductions.
-//   RECT: the warp's pixels form the 8x4 rectangle with corner pixel centre (ox, oy), lane = 8*row + col
-//   otherwise the per-lane pixel centres are read from sP.
-template <bool RECT>
-__device__ __forceinline__ void flush_slots(const float2* __restrict__ myW, const float4* __restrict__ myVo,
-                                            const float2* __restrict__ myP, int nslot, int lane, float own_x,
-                                            float own_y, int own_g, float ox, float oy, float* __restrict__ vgrad) {
-  __syncwarp();
-  const int sj = lane & 15, h = lane >> 4;
-  const float2* row = myW + sj * kSlotStride + h * 16;
-  const float4* vo = myVo + h * 16;
-  float m0 = 0.f, m1x = 0.f, m1y = 0.f, m2xx = 0.f, m2xy = 0.f, m2yy = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
-  if (RECT) {
-    float sx = 0.f, sy = 0.f, sxx = 0.f, sxy = 0.f, syy = 0.f;
-#pragma unroll
-    for (int t = 0; t < 16; ++t) {
-      const float2 wf = row[t];
-      const float4 o = vo[t];
-      const float ix = (float)(t & 7), iy = (float)(t >> 3);
-      m0 += wf.x;
-      if (t & 7) { sx = fmaf(wf.x, ix, sx); sxx = fmaf(wf.x, ix * ix, sxx); }
-      if (t >> 3) { sy = fmaf(wf.x, iy, sy); syy = fmaf(wf.x, iy * iy, syy); }
-      if ((t & 7) && (t >> 3)) sxy = fmaf(wf.x, ix * iy, sxy);
-      cr = fmaf(wf.y, o.x, cr); cg = fmaf(wf.y, o.y, cg); cb = fmaf(wf.y, o.z, cb);
-    }
-    const float ax = own_x - ox, ay = own_y - (oy + (float)(2 * h));
-    m1x = ax * m0 - sx;
-    m1y = ay * m0 - sy;
-    m2xx = ax * (m1x - sx) + sxx;
-    m2xy = ay * m1x - ax * sy + sxy;
-    m2yy = ay * (m1y - sy) + syy;
-  } else {
-    const float2* pp = myP + h * 16;
-#pragma unroll
-    for (int t = 0; t < 16; ++t) {
-      const float2 wf = row[t];
-      const float4 o = vo[t];
-      const float2 pc = pp[t];
-      const float dx = own_x - pc.x, dy = own_y - pc.y;
-      const float wdx = wf.x * dx, wdy = wf.x * dy;
-      m0 += wf.x; m1x += wdx; m1y += wdy;
-      m2xx = fmaf(wdx, dx, m2xx); m2xy = fmaf(wdx, dy, m2xy); m2yy = fmaf(wdy, dy, m2yy);
-      cr = fmaf(wf.y, o.x, cr); cg = fmaf(wf.y, o.y, cg); cb = fmaf(wf.y, o.z, cb);
-    }
-  }
-  m0 += __shfl_xor_sync(0xffffffffu, m0, 16);
-  m1x += __shfl_xor_sync(0xffffffffu, m1x, 16);
-  m1y += __shfl_xor_sync(0xffffffffu, m1y, 16);
-  m2xx += __shfl_xor_sync(0xffffffffu, m2xx, 16);
-  m2xy += __shfl_xor_sync(0xffffffffu, m2xy, 16);
-  m2yy += __shfl_xor_sync(0xffffffffu, m2yy, 16);
-  cr += __shfl_xor_sync(0xffffffffu, cr, 16);
-  cg += __shfl_xor_sync(0xffffffffu, cg, 16);
-  cb += __shfl_xor_sync(0xffffffffu, cb, 16);
-  if (h == 0 && sj < nslot) {
-    float* dst = vgrad + (size_t)own_g * 12;
-    red_add_v4(dst, m1x, m1y, m2xx, m2xy);
-    red_add_v4(dst + 4, m2yy, m0, cr, cg);
-    if (cb != 0.f) atomicAdd(dst + 8, cb);
-  }
-  __syncwarp();
-}
 
 template <bool RECT, int NW>
 __global__ void __launch_bounds__(NW * 32) raster_bwd_kernel(

@@ -1,0 +1,298 @@
+// Rect-list rasteriser (forward and backward) for the fused multi-view path, block width 16.
+// Same arithmetic per (pixel, Gaussian) pair as raster_fwd.cu / raster_bwd.cu (SURVEY.md A.5 / A.6;
+// upstream _C.rasterize_forward / _backward behind gsplat.rasterize_gaussians,
+// /root/reference/utils/gs_utils.py:96-109, train.py:289) -- what changes is who walks which list.
+//
+// sb_sort_tiles has already split every tile's depth-sorted list into eight lists, one per 8x4-pixel
+// rectangle, keeping only the Gaussians whose visible region reaches the rectangle (exact test,
+// raster_common.cuh: rect_mask).  Here ONE WARP owns one rectangle and its list:
+//   * no block-level barrier and no shared staging between warps: a warp gathers the 32 next records
+//     of ITS list lane-parallel (one 48-byte record per lane) into registers while it composites the
+//     current 32 from its private 1.5 KB of shared memory -- the gather latency hides behind the walk;
+//   * no per-warp culling pass and no ballot / find-first-set loop: every list entry is a hit, the walk
+//     is a plain counted loop over consecutive shared-memory slots;
+//   * early termination is per warp (all 32 pixels saturated), not per 256-pixel tile.
+// The CTA (8 warps = the 8 rectangles of a tile) only exists for launch granularity and for the one
+// block-level sum of the fused loss.
+#include "raster_common.cuh"
+
+namespace sb {
+
+constexpr int kRectWarps = 8;     // forward: one CTA per tile (one block-level loss sum)
+constexpr int kRectWarpsB = 4;    // backward: two CTAs per tile (shared-memory budget of the slot buffers)
+
+struct RectGeom {
+  int px_i, py_i;      // this lane's pixel
+  bool inside;
+  float px, py;        // its centre
+  float ox, oy;        // centre of the rectangle's corner pixel (lane 0)
+};
+
+__device__ __forceinline__ RectGeom rect_geom(int tile_x, int tile_y, int warp, int lane, int img_w, int img_h) {
+  RectGeom rg;
+  const int x0 = tile_x * 16 + (warp & 1) * 8, y0 = tile_y * 16 + (warp >> 1) * 4;
+  rg.px_i = x0 + (lane & 7);
+  rg.py_i = y0 + (lane >> 3);
+  rg.inside = rg.px_i < img_w && rg.py_i < img_h;
+  rg.px = (float)rg.px_i + 0.5f; rg.py = (float)rg.py_i + 0.5f;
+  rg.ox = (float)x0 + 0.5f; rg.oy = (float)y0 + 0.5f;
+  return rg;
+}
+
+__global__ void __launch_bounds__(kRectWarps * 32) raster_rect_fwd_kernel(
+    int n, const float4* __restrict__ packed, const int* __restrict__ rect_ids,
+    const int* __restrict__ rect_counts, int cap, const float* __restrict__ background, int tiles_x,
+    int tiles_y, int img_w, int img_h, const int* __restrict__ view_has_isects,
+    float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx,
+    float* __restrict__ out_alpha, int clamp_rgb, const void* __restrict__ gt, int gt_u8,
+    float* __restrict__ loss_partial) {
+  __shared__ float4 sRec[kRectWarps][3][32];
+  const int tile = blockIdx.x, v = blockIdx.y;
+  const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const RectGeom rg = rect_geom(tile_x, tile_y, warp, lane, img_w, img_h);
+  const size_t rect = ((size_t)v * tiles_x * tiles_y + tile) * 8 + warp;
+  const int count = __ldg(rect_counts + rect);
+  const int* ids = rect_ids + rect * cap;
+  const float4* vp = packed + (size_t)v * n * 3;
+  float4* sA = sRec[warp][0];
+  float4* sB = sRec[warp][1];
+  float4* sC = sRec[warp][2];
+
+  float T = 1.0f, pr = 0.f, pg = 0.f, pb = 0.f;
+  int cur_idx = -1;
+  bool done = !rg.inside;
+
+  // registers hold the records of the NEXT 32 list entries
+  float4 rA = make_float4(0.f, 0.f, 0.f, 0.f), rB = rA, rC = rA;
+  if (lane < count) {
+    const float4* p = vp + (size_t)__ldg(ids + lane) * 3;
+    rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
+  }
+  for (int c0 = 0; c0 < count; c0 += 32) {
+    __syncwarp();
+    sA[lane] = rA; sB[lane] = rB; sC[lane] = rC;
+    __syncwarp();
+    if (c0 + 32 + lane < count) {
+      const float4* p = vp + (size_t)__ldg(ids + c0 + 32 + lane) * 3;
+      rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
+    }
+    const int m = min(32, count - c0);
+#pragma unroll 4
+    for (int k = 0; k < m; ++k) {
+      const float4 A = sA[k], B = sB[k], C = sC[k];
+      const float dx = A.x - rg.px, dy = A.y - rg.py;
+      const float pw = dx * fmaf(B.y, dy, B.x * dx) + B.z * dy * dy;      // -sigma * log2(e)
+      const float alpha = fminf(kAlphaMax, ex2_approx(pw + B.w));
+      const bool valid = !done && (pw <= 0.f) && (alpha >= kAlphaMin);
+      const float next_T = T * (1.0f - alpha);
+      const bool stop = valid && (next_T <= kTMin);
+      const bool upd = valid && !stop;
+      done = done || stop;
+      const float wgt = upd ? alpha * T : 0.f;
+      pr = fmaf(C.x, wgt, pr); pg = fmaf(C.y, wgt, pg); pb = fmaf(C.z, wgt, pb);
+      T = upd ? next_T : T;
+      cur_idx = upd ? c0 + k : cur_idx;
+    }
+    if (__all_sync(0xffffffffu, done)) break;
+  }
+
+  float l1 = 0.f, l2 = 0.f;
+  if (rg.inside) {
+    const size_t pix = ((size_t)v * img_h + rg.py_i) * img_w + rg.px_i;
+    // upstream quirk: a view without a single intersection reports final_T = 0
+    // (alpha = 1) while its image is the plain background
+    const bool empty_view = view_has_isects ? __ldg(view_has_isects + v) == 0 : false;
+    float r = pr + T * __ldg(background), g = pg + T * __ldg(background + 1), b = pb + T * __ldg(background + 2);
+    if (clamp_rgb) { r = fminf(r, 1.0f); g = fminf(g, 1.0f); b = fminf(b, 1.0f); }   // gs_utils.py:111
+    final_ts[pix] = empty_view ? 0.f : T;
+    final_idx[pix] = cur_idx;
+    if (out_alpha) out_alpha[pix] = empty_view ? 1.f : 1.0f - T;
+    out_img[3 * pix] = r; out_img[3 * pix + 1] = g; out_img[3 * pix + 2] = b;
+    if (gt) {
+      float tr, tg, tb;
+      load_gt(gt, gt_u8, pix, tr, tg, tb);
+      const float dr = r - tr, dg = g - tg, db = b - tb;
+      l1 = fabsf(dr) + fabsf(dg) + fabsf(db);
+      l2 = dr * dr + dg * dg + db * db;
+    }
+  }
+  if (loss_partial) {
+    // fused L1 / squared-error partial sums of the tile (train.py:275,278): one deterministic
+    // (V, T, 2) entry per CTA, summed by the caller
+    __shared__ float sRed[2][kRectWarps];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      l1 += __shfl_xor_sync(0xffffffffu, l1, o);
+      l2 += __shfl_xor_sync(0xffffffffu, l2, o);
+    }
+    if (lane == 0) { sRed[0][warp] = l1; sRed[1][warp] = l2; }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < kRectWarps; ++w) t += sRed[threadIdx.x][w];
+      loss_partial[((size_t)v * tiles_x * tiles_y + tile) * 2 + threadIdx.x] = t;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward: every warp walks its rectangle's list from the last composited entry back to the front.
+// Gradient sums leave the warp through the transposed shared-memory reduction (raster_common.cuh:
+// flush_slots): 16 parked hits per flush, two red.global.add.v4.f32 + one scalar red per hit.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kRectWarpsB * 32, 8) raster_rect_bwd_kernel(
+    int n, const float4* __restrict__ packed, const int* __restrict__ rect_ids,
+    const int* __restrict__ rect_counts, int cap, const float* __restrict__ background, int tiles_x,
+    int tiles_y, int img_w, int img_h, int clamped, const float* __restrict__ final_ts,
+    const int* __restrict__ final_idx, const float* __restrict__ v_out_img,
+    const float* __restrict__ v_out_alpha, const float* __restrict__ out_img,
+    const void* __restrict__ gt, int gt_u8, const float* __restrict__ v_loss, float* __restrict__ v_packed) {
+  __shared__ float4 sRec[kRectWarpsB][3][32];
+  __shared__ int sGid[kRectWarpsB][32];
+  __shared__ float4 sVo[kRectWarpsB][32];
+  __shared__ float2 sW[kRectWarpsB][kSlots * kSlotStride];
+  constexpr int kParts = 8 / kRectWarpsB;
+  const int tile = blockIdx.x / kParts, v = blockIdx.y;
+  const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wt = warp + (blockIdx.x % kParts) * kRectWarpsB;        // rectangle index within the tile
+  const RectGeom rg = rect_geom(tile_x, tile_y, wt, lane, img_w, img_h);
+  const size_t rect = ((size_t)v * tiles_x * tiles_y + tile) * 8 + wt;
+  const int count = __ldg(rect_counts + rect);
+  if (count <= 0) return;
+  const int* ids = rect_ids + rect * cap;
+  const float4* vp = packed + (size_t)v * n * 3;
+  float* vgrad = v_packed + (size_t)v * n * 12;
+  float4* sA = sRec[warp][0];
+  float4* sB = sRec[warp][1];
+  float4* sC = sRec[warp][2];
+  int* sG = sGid[warp];
+
+  float T_final = 1.f, vo_r = 0.f, vo_g = 0.f, vo_b = 0.f, vo_a = 0.f;
+  int last = -1;
+  if (rg.inside) {
+    const size_t pix = ((size_t)v * img_h + rg.py_i) * img_w + rg.px_i;
+    T_final = __ldg(final_ts + pix);
+    last = __ldg(final_idx + pix);
+    if (v_out_img) {
+      vo_r = __ldg(v_out_img + 3 * pix); vo_g = __ldg(v_out_img + 3 * pix + 1); vo_b = __ldg(v_out_img + 3 * pix + 2);
+    }
+    if (v_out_alpha) vo_a = __ldg(v_out_alpha + pix);
+    if (gt) {
+      // fused L1 loss (train.py:275): d|x - gt|/dx = sign(x - gt), scaled by the upstream gradient of
+      // this view's loss term
+      const float sc = __ldg(v_loss + v);
+      float tr, tg, tb;
+      load_gt(gt, gt_u8, pix, tr, tg, tb);
+      const float dr = __ldg(out_img + 3 * pix) - tr;
+      const float dg = __ldg(out_img + 3 * pix + 1) - tg;
+      const float db = __ldg(out_img + 3 * pix + 2) - tb;
+      vo_r += dr > 0.f ? sc : (dr < 0.f ? -sc : 0.f);
+      vo_g += dg > 0.f ? sc : (dg < 0.f ? -sc : 0.f);
+      vo_b += db > 0.f ? sc : (db < 0.f ? -sc : 0.f);
+    }
+    if (out_img && clamped) {
+      // the forward stored min(rgb, 1) (gs_utils.py:111): no gradient through a clamped channel
+      if (!(__ldg(out_img + 3 * pix) < 1.0f)) vo_r = 0.f;
+      if (!(__ldg(out_img + 3 * pix + 1) < 1.0f)) vo_g = 0.f;
+      if (!(__ldg(out_img + 3 * pix + 2) < 1.0f)) vo_b = 0.f;
+    }
+  }
+  const int warp_last = __reduce_max_sync(0xffffffffu, last);
+  if (warp_last < 0) return;                      // nothing was composited in this rectangle
+  sVo[warp][lane] = make_float4(vo_r, vo_g, vo_b, 0.f);
+  const float bg_dot = __ldg(background) * vo_r + __ldg(background + 1) * vo_g + __ldg(background + 2) * vo_b;
+  // v_alpha = T * (rgb . v_out) - ra * acc,  acc = sum_{behind} fac_j (rgb_j . v_out) - T_final (v_out_alpha - bg . v_out)
+  float T = T_final;
+  float acc = -T_final * (vo_a - bg_dot);
+  int nslot = 0;
+  float own_x = 0.f, own_y = 0.f;
+  int own_g = 0;
+
+  // chunk c covers list positions [32c, 32c + 32); slot s of a chunk holds position 32c + s
+  int c = warp_last >> 5;
+  float4 rA = make_float4(0.f, 0.f, 0.f, 0.f), rB = rA, rC = rA;
+  int rG = 0;
+  if (32 * c + lane <= warp_last) {
+    rG = __ldg(ids + 32 * c + lane);
+    const float4* p = vp + (size_t)rG * 3;
+    rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
+  }
+  for (; c >= 0; --c) {
+    __syncwarp();
+    sA[lane] = rA; sB[lane] = rB; sC[lane] = rC; sG[lane] = rG;
+    __syncwarp();
+    if (c > 0) {
+      rG = __ldg(ids + 32 * (c - 1) + lane);
+      const float4* p = vp + (size_t)rG * 3;
+      rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
+    }
+    const int top = min(31, warp_last - 32 * c);
+    for (int k = top; k >= 0; --k) {
+      const int idx = 32 * c + k;
+      const float4 A = sA[k], B = sB[k];
+      const float dx = A.x - rg.px, dy = A.y - rg.py;
+      const float pw = dx * fmaf(B.y, dy, B.x * dx) + B.z * dy * dy;
+      const float alpha_raw = ex2_approx(pw + B.w);
+      const float alpha = fminf(kAlphaMax, alpha_raw);
+      const bool valid = (idx <= last) && (pw <= 0.f) && (alpha >= kAlphaMin);
+      if (!__any_sync(0xffffffffu, valid)) continue;
+      const float4 C = sC[k];
+      const float ra = rcp_approx(1.0f - alpha);
+      T = valid ? T * ra : T;
+      const float fac = valid ? alpha * T : 0.f;
+      const float cdot = C.x * vo_r + C.y * vo_g + C.z * vo_b;
+      const float v_alpha = T * cdot - ra * acc;
+      acc = fmaf(fac, cdot, acc);
+      // d alpha / d sigma = -alpha_raw where the 0.999 clamp is inactive, 0 where it is active
+      const float w = (valid && alpha_raw <= kAlphaMax) ? -alpha_raw * v_alpha : 0.f;
+      sW[warp][nslot * kSlotStride + lane] = make_float2(w, fac);
+      if ((lane & 15) == nslot) { own_x = A.x; own_y = A.y; own_g = sG[k]; }
+      if (++nslot == kSlots) {
+        flush_slots<true>(sW[warp], sVo[warp], nullptr, kSlots, lane, own_x, own_y, own_g, rg.ox, rg.oy, vgrad);
+        nslot = 0;
+      }
+    }
+  }
+  if (nslot) flush_slots<true>(sW[warp], sVo[warp], nullptr, nslot, lane, own_x, own_y, own_g, rg.ox, rg.oy, vgrad);
+}
+
+}  // namespace sb
+
+extern "C" int sb_rasterize_rect_fwd(int num_views, int n, const float* packed, const int* rect_ids,
+                                     const int* rect_counts, int rect_capacity, const float* background,
+                                     int img_h, int img_w, const int* view_has_isects, float* out_img,
+                                     float* final_ts, int* final_idx, float* out_alpha,
+                                     int clamp_rgb_max1, const void* gt, int gt_is_u8,
+                                     float* loss_partial, sb_stream_t stream) {
+  if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || rect_capacity < 1 || (loss_partial && !gt))
+    return SB_ERR_BAD_ARG;
+  const int tiles_x = sb::ceil_div(img_w, 16), tiles_y = sb::ceil_div(img_h, 16);
+  dim3 grid(tiles_x * tiles_y, num_views);
+  sb::raster_rect_fwd_kernel<<<grid, sb::kRectWarps * 32, 0, (cudaStream_t)stream>>>(
+      n, reinterpret_cast<const float4*>(packed), rect_ids, rect_counts, rect_capacity, background, tiles_x,
+      tiles_y, img_w, img_h, view_has_isects, out_img, final_ts, final_idx, out_alpha, clamp_rgb_max1, gt,
+      gt_is_u8, loss_partial);
+  SB_RETURN_LAST();
+}
+
+extern "C" int sb_rasterize_rect_bwd(int num_views, int n, const float* packed, const int* rect_ids,
+                                     const int* rect_counts, int rect_capacity, const float* background,
+                                     int img_h, int img_w, const float* final_ts, const int* final_idx,
+                                     const float* v_out_img, const float* v_out_alpha,
+                                     const float* out_img, int clamped_rgb_max1, const void* gt,
+                                     int gt_is_u8, const float* v_loss, float* v_packed,
+                                     sb_stream_t stream) {
+  if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || rect_capacity < 1 ||
+      (!v_out_img && !gt && !v_out_alpha) || (gt && (!out_img || !v_loss)) || (clamped_rgb_max1 && !out_img))
+    return SB_ERR_BAD_ARG;
+  const int tiles_x = sb::ceil_div(img_w, 16), tiles_y = sb::ceil_div(img_h, 16);
+  dim3 grid(tiles_x * tiles_y * (8 / sb::kRectWarpsB), num_views);
+  sb::raster_rect_bwd_kernel<<<grid, sb::kRectWarpsB * 32, 0, (cudaStream_t)stream>>>(
+      n, reinterpret_cast<const float4*>(packed), rect_ids, rect_counts, rect_capacity, background, tiles_x,
+      tiles_y, img_w, img_h, clamped_rgb_max1, final_ts, final_idx, v_out_img, v_out_alpha, out_img, gt,
+      gt_is_u8, v_loss, v_packed);
+  SB_RETURN_LAST();
+}

@@ -13,7 +13,7 @@
 // intersections, so the forward pass needs no synchronisation before the raster kernel.
 // Traffic: 8 bytes written + 8 read + 4 written per intersection instead of a scan, a 12-byte
 // emission and six radix passes over 12-byte pairs.
-#include "sb_common.cuh"
+#include "raster_common.cuh"
 
 namespace sb {
 
@@ -53,7 +53,9 @@ __global__ void __launch_bounds__(kSortBlock) sort_tiles_kernel(int cap, int til
                                                                 const int* __restrict__ counts,
                                                                 const unsigned long long* __restrict__ keys,
                                                                 int* __restrict__ gids_sorted, int2* __restrict__ bins,
-                                                                int* __restrict__ view_has, int* __restrict__ totals) {
+                                                                int* __restrict__ view_has, int* __restrict__ totals,
+                                                                int n, int tiles_x, const float4* __restrict__ packed,
+                                                                int* __restrict__ rect_ids, int* __restrict__ rect_counts) {
   extern __shared__ unsigned long long s_keys[];
   int* s_end = reinterpret_cast<int*>(s_keys + cap);
   __shared__ unsigned s_min, s_max;
@@ -67,7 +69,10 @@ __global__ void __launch_bounds__(kSortBlock) sort_tiles_kernel(int cap, int til
     if (len > 0) { view_has[blockIdx.x / tiles_per_view] = 1; atomicAdd(totals, len); }
     if (count > cap) totals[1] = 1;
   }
-  if (len <= 0) return;
+  if (len <= 0) {
+    if (rect_counts && threadIdx.x < 8) rect_counts[(size_t)blockIdx.x * 8 + threadIdx.x] = 0;
+    return;
+  }
   const unsigned long long* src = keys + range.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (len <= 32) {
@@ -76,10 +81,10 @@ __global__ void __launch_bounds__(kSortBlock) sort_tiles_kernel(int cap, int til
       const unsigned long long mine = lane < len ? __ldg(src + lane) : ~0ull;
       int rank = 0;
       for (int o = 0; o < len; ++o) rank += __shfl_sync(0xffffffffu, mine, o) < mine;
-      if (lane < len) gids_sorted[range.x + rank] = (int)(unsigned)(mine & 0xffffffffull);
+      if (lane < len) s_keys[rank] = mine;
     }
-    return;
-  }
+    __syncthreads();
+  } else {
   int nb = 64;                             // buckets: power of two >= len
   while (nb < len) nb <<= 1;
   // pass 1: depth-bit range of the tile
@@ -152,7 +157,70 @@ __global__ void __launch_bounds__(kSortBlock) sort_tiles_kernel(int cap, int til
     }
     __syncthreads();
   }
-  for (int i = threadIdx.x; i < len; i += kSortBlock) gids_sorted[range.x + i] = (int)(unsigned)(s_keys[i] & 0xffffffffull);
+  }   // len > 32
+  if (gids_sorted)
+    for (int i = threadIdx.x; i < len; i += kSortBlock) gids_sorted[range.x + i] = (int)(unsigned)(s_keys[i] & 0xffffffffull);
+  if (!rect_ids) return;
+
+  // ---- rect lists: for each of the tile's eight 8x4 rectangles, the depth-ordered ids of the Gaussians
+  // whose visible region reaches it (raster_common.cuh: rect_mask), compacted stably per rectangle into
+  // rect_ids[(tile * 8 + r) * cap + ...]; the rect-list rasteriser gives every rectangle to one warp.
+  // Entry i belongs to slot (i / 256, warp): phase A computes every entry's 8-bit mask and the per-slot
+  // counts, one warp per rectangle then scans the slot counts, phase C writes the ids.  The bucket
+  // table s_end is free by now and holds the masks (cap bytes) and the slot counts (cap bytes).
+  unsigned char* s_mask = reinterpret_cast<unsigned char*>(s_end);
+  int* s_cnt = s_end + (cap >> 2);                 // [slot][8], slot = chunk * 8 + warp
+  const int v = blockIdx.x / tiles_per_view, tile = blockIdx.x - v * tiles_per_view;
+  const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
+  const float4* vp = packed + (size_t)v * n * 3;
+  int* out = rect_ids + (size_t)blockIdx.x * 8 * cap;
+  const int nchunks = (len + kSortBlock - 1) / kSortBlock;
+  __syncthreads();                                 // everyone is done with s_end as the bucket table
+  for (int c = 0; c < nchunks; ++c) {
+    const int i = c * kSortBlock + threadIdx.x;
+    unsigned mask = 0u;
+    if (i < len) {
+      const float4* rec = vp + (size_t)(unsigned)(s_keys[i] & 0xffffffffull) * 3;
+      mask = rect_mask(__ldg(rec), __ldg(rec + 1), tile_x, tile_y);
+      s_mask[i] = (unsigned char)mask;
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const unsigned bal = __ballot_sync(0xffffffffu, (mask >> r) & 1u);
+      if (lane == r) s_cnt[(c * 8 + warp) * 8 + r] = __popc(bal);
+    }
+  }
+  __syncthreads();
+  {
+    // warp r: exclusive scan of rectangle r's slot counts, in slot order
+    const int r = warp, nslots = nchunks * 8;
+    int carry = 0;
+    for (int j0 = 0; j0 < nslots; j0 += 32) {
+      const int j = j0 + lane;
+      const int cnt = j < nslots ? s_cnt[j * 8 + r] : 0;
+      int x = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+      }
+      if (j < nslots) s_cnt[j * 8 + r] = carry + x - cnt;
+      carry += __shfl_sync(0xffffffffu, x, 31);
+    }
+    if (lane == 0) rect_counts[(size_t)blockIdx.x * 8 + r] = carry;
+  }
+  __syncthreads();
+  for (int c = 0; c < nchunks; ++c) {
+    const int i = c * kSortBlock + threadIdx.x;
+    const unsigned mask = i < len ? s_mask[i] : 0u;
+    const int g = i < len ? (int)(unsigned)(s_keys[i] & 0xffffffffull) : 0;
+    const int* pre = s_cnt + (c * 8 + warp) * 8;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const unsigned bal = __ballot_sync(0xffffffffu, (mask >> r) & 1u);
+      if ((mask >> r) & 1u) out[(size_t)r * cap + pre[r] + __popc(bal & ((1u << lane) - 1u))] = g;
+    }
+  }
 }
 
 }  // namespace sb
@@ -161,16 +229,19 @@ extern "C" int sb_tile_sort_capacity(void) { return sb::kMaxSegment; }
 
 extern "C" int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, const int* tile_counts,
                              const uint64_t* tile_keys, int* gaussian_ids_sorted, int* tile_bins,
-                             int* view_has_isects, int* totals, sb_stream_t stream) {
+                             int* view_has_isects, int* totals, int n, int tiles_x, const float* packed,
+                             int* rect_ids, int* rect_counts, sb_stream_t stream) {
   if (num_views < 1 || tiles_per_view < 1 || tile_capacity < 64 || tile_capacity > sb::kMaxSegment ||
       (tile_capacity & (tile_capacity - 1)) ||
-      (long long)num_views * tiles_per_view * tile_capacity > 2147483647LL)
+      (long long)num_views * tiles_per_view * tile_capacity > 2147483647LL ||
+      (rect_ids && (!packed || !rect_counts || tiles_x < 1 || tiles_per_view % tiles_x)))
     return SB_ERR_BAD_ARG;
   const size_t smem = (size_t)tile_capacity * 12;
   if (smem > 40 * 1024)      // the kernel also has a little static shared memory
     cudaFuncSetAttribute(sb::sort_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   sb::sort_tiles_kernel<<<num_views * tiles_per_view, sb::kSortBlock, smem, (cudaStream_t)stream>>>(
       tile_capacity, tiles_per_view, tile_counts, reinterpret_cast<const unsigned long long*>(tile_keys),
-      gaussian_ids_sorted, reinterpret_cast<int2*>(tile_bins), view_has_isects, totals);
+      gaussian_ids_sorted, reinterpret_cast<int2*>(tile_bins), view_has_isects, totals, n, tiles_x,
+      reinterpret_cast<const float4*>(packed), rect_ids, rect_counts);
   SB_RETURN_LAST();
 }

@@ -83,6 +83,7 @@ def _c(t: Tensor) -> Tensor:
 _side_streams: Dict[int, torch.cuda.Stream] = {}
 _pinned: Dict[int, Tensor] = {}
 _overflowed: Dict[Tuple[int, int, int], int] = {}
+USE_RECT_LISTS = True               # fused path, block width 16: rect-list rasteriser (csrc/raster_rect.cu)
 DEFAULT_TILE_CAPACITY = 2048        # doubled per overflow of a (views, tiles, Gaussians) shape, up to the library's limit
 
 
@@ -181,6 +182,19 @@ class _RenderViews(Function):
                     _abi.ptr(tile_counts, I32, "tile_counts"), _abi.ptr(tile_keys, torch.int64, "tile_keys"), cap,
                     _abi.stream()), "sb_views_project_fwd")
 
+        def raster_rect(rect_ids, rect_counts, cap, view_has):
+            if gt_ready is not None:
+                torch.cuda.current_stream().wait_event(gt_ready)
+            with _stage("raster_fwd"):
+                _abi.check(lib.sb_rasterize_rect_fwd(
+                    v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(rect_ids, I32, "rect_ids"),
+                    _abi.ptr(rect_counts, I32, "rect_counts"), cap, _abi.ptr(background, F32, "background"),
+                    img_height, img_width, _abi.ptr(view_has, I32, "view_has_isects"),
+                    _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
+                    _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
+                    1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,
+                    _abi.ptr(loss_partial, F32, "loss_partial"), _abi.stream()), "sb_rasterize_rect_fwd")
+
         def raster(gids_sorted, tile_bins, view_has):
             if gt_ready is not None:
                 torch.cuda.current_stream().wait_event(gt_ready)
@@ -197,6 +211,7 @@ class _RenderViews(Function):
         global _last_num_intersects
         cap = _tile_capacity(lib, v, num_tiles, n)
         done = False
+        rect_ids = rect_counts = None
         if cap:
             # fixed-capacity tile segments + per-tile sort (csrc/tile_sort.cu).  The raster kernel is
             # enqueued optimistically; the host then reads the overflow flag, which the GPU produced
@@ -207,23 +222,34 @@ class _RenderViews(Function):
             tile_keys = torch.empty(v * num_tiles * cap, dtype=torch.int64, device=dev)
             gids_sorted = torch.empty(v * num_tiles * cap, dtype=I32, device=dev)
             tile_bins = torch.empty(v * num_tiles, 2, dtype=I32, device=dev)
+            use_rect = block_width == 16 and USE_RECT_LISTS
+            if use_rect:
+                # per-rectangle lists for the rect-list rasteriser (one warp per 8x4 rectangle)
+                rect_ids = torch.empty(v * num_tiles * 8 * cap, dtype=I32, device=dev)
+                rect_counts = torch.empty(v * num_tiles * 8, dtype=I32, device=dev)
             project(tile_counts, tile_keys, cap)
             with _stage("sort_tiles"):
                 _abi.check(lib.sb_sort_tiles(
                     v, num_tiles, cap, _abi.ptr(tile_counts, I32, "tile_counts"),
                     _abi.ptr(tile_keys, torch.int64, "tile_keys"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
                     _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(view_has, I32, "view_has_isects"),
-                    _abi.ptr(totals, I32, "totals"), _abi.stream()), "sb_sort_tiles")
+                    _abi.ptr(totals, I32, "totals"), n, tiles_x, _abi.ptr(packed, F32, "packed"),
+                    _abi.ptr(rect_ids, I32, "rect_ids"), _abi.ptr(rect_counts, I32, "rect_counts"),
+                    _abi.stream()), "sb_sort_tiles")
             host_totals = _pinned_pair(dev)
             host_totals.copy_(totals, non_blocking=True)
             flag_ready = torch.cuda.Event()
             flag_ready.record()
-            raster(gids_sorted, tile_bins, view_has)
+            if use_rect:
+                raster_rect(rect_ids, rect_counts, cap, view_has)
+            else:
+                raster(gids_sorted, tile_bins, view_has)
             flag_ready.synchronize()
             num_intersects, overflow = int(host_totals[0]), int(host_totals[1])
             done = overflow == 0
             if not done:
                 _note_overflow(v, num_tiles, n)
+                rect_ids = rect_counts = None
         if not done:
             # very deep tiles: global 64-bit (tile | depth) radix sort, as the per-view API does
             if not cap:
@@ -243,10 +269,11 @@ class _RenderViews(Function):
         _last_num_intersects = num_intersects
         ctx.meta = (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride,
                     tuple(color_src.shape), None if color_rest is None else tuple(color_rest.shape),
-                    num_intersects, clamp_rgb)
+                    num_intersects, clamp_rgb, cap)
         keep_img = clamp_rgb or gt is not None
         ctx.save_for_backward(means, scales, quats, viewmats, campos, intrins, background, packed,
-                              gids_sorted, tile_bins, final_ts, final_idx, out_img if keep_img else None, gt)
+                              gids_sorted, tile_bins, final_ts, final_idx, out_img if keep_img else None, gt,
+                              rect_ids, rect_counts)
         ctx.set_materialize_grads(False)
         if gt is not None:
             sums = loss_partial.sum(dim=1)                       # (V, 2): sum |rgb - gt|, sum (rgb - gt)^2
@@ -259,9 +286,9 @@ class _RenderViews(Function):
     def backward(ctx, *grads):
         lib = _abi.load()
         (means, scales, quats, viewmats, campos, intrins, background, packed, gids_sorted, tile_bins,
-         final_ts, final_idx, out_img, gt) = ctx.saved_tensors
+         final_ts, final_idx, out_img, gt, rect_ids, rect_counts) = ctx.saved_tensors
         (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride, color_shape,
-         rest_shape, num_intersects, clamp_rgb) = ctx.meta
+         rest_shape, num_intersects, clamp_rgb, cap) = ctx.meta
         dev = means.device
         nin = 18
         if gt is not None:
@@ -279,7 +306,20 @@ class _RenderViews(Function):
             v_loss = None
         with _stage("zero_grads"):
             v_packed = torch.zeros(v, n, 12, dtype=F32, device=dev)
-        with _stage("raster_bwd"):
+        gt_dt = None if gt is None else gt.dtype
+        if rect_ids is not None:
+            with _stage("raster_bwd"):
+                _abi.check(lib.sb_rasterize_rect_bwd(
+                    v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(rect_ids, I32, "rect_ids"),
+                    _abi.ptr(rect_counts, I32, "rect_counts"), cap, _abi.ptr(background, F32, "background"),
+                    img_height, img_width, _abi.ptr(final_ts, F32, "final_Ts"),
+                    _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(v_out_img, F32, "v_out_img"),
+                    _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(out_img, F32, "out_img"),
+                    1 if clamp_rgb else 0, _abi.ptr(gt, gt_dt, "gt"), 1 if gt_dt == torch.uint8 else 0,
+                    _abi.ptr(v_loss, F32, "v_loss"), _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()),
+                    "sb_rasterize_rect_bwd")
+        else:
+          with _stage("raster_bwd"):
             _abi.check(lib.sb_rasterize_bwd(
                 v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
                 _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,

@@ -175,7 +175,8 @@ SB_API int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, c
  * A 16x16 tile is eight 8x4-pixel rectangles (rect r: columns 8*(r&1).., rows 4*(r>>1)..).  Given
  * rect_ids (V*T*8*capacity) and rect_counts (V*T*8), sb_sort_tiles additionally writes, for every
  * rectangle, the depth-ordered ids of the Gaussians whose {alpha >= 1/255} region reaches it (exact
- * ellipse / rectangle test, conservatively inflated) into rect_ids[(tile*8 + r)*capacity + ...]
+ * ellipse / rectangle test on the packed records, conservatively inflated) into
+ * rect_ids[(tile*8 + r)*capacity + ...]
  * (gaussian_ids_sorted may then be NULL).  The two kernels below give each rectangle to one warp,
  * which walks its own list with no block-level synchronisation: same compositing order, same images
  * and gradients as sb_rasterize_fwd / _bwd (the dropped pairs are ones those kernels skip).

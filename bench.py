@@ -363,6 +363,13 @@ def main() -> None:
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"
         per_view = stage_bytes_per_view(n, K, isect_per_view, H * W, tiles)
+        # DRAM bytes per launch of each kernel from the committed ncu --set full capture of this same
+        # command (profiles/ncu_traffic.json); only valid for the captured shape (32 views per launch)
+        traffic = {}
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        except Exception:
+            pass
         top = max(stage_ms, key=stage_ms.get) if stage_ms else None
         roofline = None
         stages = {}
@@ -373,10 +380,14 @@ def main() -> None:
             if name in per_view:
                 gbs = per_view[name] * v_local / (avg_ms * 1e-3) / 1e9
                 entry.update(alg_bytes_per_launch=per_view[name] * v_local, gbs=gbs, frac=gbs / peak)
+            if name in traffic and v_local == 32 and V == 32:
+                entry["dram_bytes_per_launch_ncu"] = traffic[name]
             stages[name] = entry
         if top and top in per_view:
             roofline = {"kernel": top, "bound": "hbm", "achieved": stages[top]["gbs"], "peak": peak, "unit": "GB/s",
-                        "frac": stages[top]["frac"], "traffic": None, "peak_source": peak_src,
+                        "frac": stages[top]["frac"], "traffic": stages[top].get("dram_bytes_per_launch_ncu"),
+                        "traffic_source": traffic.get("_source") if stages[top].get("dram_bytes_per_launch_ncu") else None,
+                        "peak_source": peak_src,
                         "alg_bytes_per_launch": stages[top]["alg_bytes_per_launch"],
                         "ms_per_launch": stages[top]["ms_per_launch"], "views_per_launch": v_local}
         b_alg_view = sum(per_view.values())

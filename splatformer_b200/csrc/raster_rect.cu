@@ -39,6 +39,31 @@ __device__ __forceinline__ RectGeom rect_geom(int tile_x, int tile_y, int warp, 
   return rg;
 }
 
+// Shared-memory layout of a staged chunk of 32 list entries: 16 PAIRS of consecutive entries (2j, 2j+1),
+// interleaved so that one LDS.128 feeds both halves of the packed-FP32 instructions:
+//   q0[j] = { x0 x1 | y0 y1 }   q1[j] = { A0 A1 | B0 B1 }   q2[j] = { C0 C1 | lop0 lop1 }
+//   q3[j] = { r0 g0 | r1 g1 }   q4[j] = { b0 b1 }        (r, g accumulate with one packed FMA per entry)
+// A list position past the end of the list holds lop = -inf-like, i.e. alpha = 0: never composited.
+struct PairSlots {
+  float4 q0[16], q1[16], q2[16], q3[16];
+  float4 q4[16];     // .xy used; float4 stride keeps one index register for all five arrays
+};
+constexpr float kNullLop = -1.0e30f;
+
+// lane = list entry of the chunk: scatter its record into the pair layout
+__device__ __forceinline__ void stage_pair_slots(PairSlots& sl, int lane, const float4& rA, const float4& rB,
+                                                 const float4& rC) {
+  const int j = lane >> 1, h = lane & 1;
+  float* f0 = reinterpret_cast<float*>(sl.q0 + j) + h;
+  float* f1 = reinterpret_cast<float*>(sl.q1 + j) + h;
+  float* f2 = reinterpret_cast<float*>(sl.q2 + j) + h;
+  f0[0] = rA.x; f0[2] = rA.y;
+  f1[0] = rB.x; f1[2] = rB.y;
+  f2[0] = rB.z; f2[2] = rB.w;
+  *reinterpret_cast<float2*>(reinterpret_cast<float*>(sl.q3 + j) + 2 * h) = make_float2(rC.x, rC.y);
+  reinterpret_cast<float*>(sl.q4 + j)[h] = rC.z;
+}
+
 __global__ void __launch_bounds__(kRectWarps * 32) raster_rect_fwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ rect_ids,
     const int* __restrict__ rect_counts, int cap, const float* __restrict__ background, int tiles_x,
@@ -46,7 +71,7 @@ __global__ void __launch_bounds__(kRectWarps * 32) raster_rect_fwd_kernel(
     float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx,
     float* __restrict__ out_alpha, int clamp_rgb, const void* __restrict__ gt, int gt_u8,
     float* __restrict__ loss_partial) {
-  __shared__ float4 sRec[kRectWarps][3][32];
+  __shared__ PairSlots sSlots[kRectWarps];
   const int tile = blockIdx.x, v = blockIdx.y;
   const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -55,48 +80,75 @@ __global__ void __launch_bounds__(kRectWarps * 32) raster_rect_fwd_kernel(
   const int count = __ldg(rect_counts + rect);
   const int* ids = rect_ids + rect * cap;
   const float4* vp = packed + (size_t)v * n * 3;
-  float4* sA = sRec[warp][0];
-  float4* sB = sRec[warp][1];
-  float4* sC = sRec[warp][2];
+  PairSlots& sl = sSlots[warp];
 
-  float T = 1.0f, pr = 0.f, pg = 0.f, pb = 0.f;
+  float T = 1.0f, pb = 0.f;
+  unsigned long long prg = pk2(0.f, 0.f);        // (red, green) accumulators, one FFMA2 per entry
   int cur_idx = -1;
   bool done = !rg.inside;
+  const unsigned long long px2 = pk2(rg.px, rg.px), py2 = pk2(rg.py, rg.py);
 
   // registers hold the records of the NEXT 32 list entries
-  float4 rA = make_float4(0.f, 0.f, 0.f, 0.f), rB = rA, rC = rA;
+  const float4 nullA = make_float4(0.f, 0.f, 0.f, 0.f), nullB = make_float4(0.f, 0.f, 0.f, kNullLop);
+  float4 rA = nullA, rB = nullB, rC = nullA;
   if (lane < count) {
     const float4* p = vp + (size_t)__ldg(ids + lane) * 3;
     rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
   }
   for (int c0 = 0; c0 < count; c0 += 32) {
     __syncwarp();
-    sA[lane] = rA; sB[lane] = rB; sC[lane] = rC;
+    stage_pair_slots(sl, lane, rA, rB, rC);
     __syncwarp();
+    rB = nullB;
     if (c0 + 32 + lane < count) {
       const float4* p = vp + (size_t)__ldg(ids + c0 + 32 + lane) * 3;
       rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
     }
-    const int m = min(32, count - c0);
+    const int npairs = (min(32, count - c0) + 1) >> 1;
 #pragma unroll 4
-    for (int k = 0; k < m; ++k) {
-      const float4 A = sA[k], B = sB[k], C = sC[k];
-      const float dx = A.x - rg.px, dy = A.y - rg.py;
-      const float pw = dx * fmaf(B.y, dy, B.x * dx) + B.z * dy * dy;      // -sigma * log2(e)
-      const float alpha = fminf(kAlphaMax, ex2_approx(pw + B.w));
-      const bool valid = !done && (pw <= 0.f) && (alpha >= kAlphaMin);
-      const float next_T = T * (1.0f - alpha);
-      const bool stop = valid && (next_T <= kTMin);
-      const bool upd = valid && !stop;
-      done = done || stop;
-      const float wgt = upd ? alpha * T : 0.f;
-      pr = fmaf(C.x, wgt, pr); pg = fmaf(C.y, wgt, pg); pb = fmaf(C.z, wgt, pb);
-      T = upd ? next_T : T;
-      cur_idx = upd ? c0 + k : cur_idx;
+    for (int j = 0; j < npairs; ++j) {
+      const float4 Q0 = sl.q0[j], Q1 = sl.q1[j], Q2 = sl.q2[j];
+      // both entries of the pair at once; every half rounds exactly like the scalar expression
+      //   pw = dx * fma(B, dy, A * dx) + (C * dy) * dy,   log2(alpha) = pw + lop
+      const unsigned long long dx2 = sub2(pk2(Q0.x, Q0.y), px2), dy2 = sub2(pk2(Q0.z, Q0.w), py2);
+      const unsigned long long t2 = fma2(pk2(Q1.z, Q1.w), dy2, mul2(pk2(Q1.x, Q1.y), dx2));
+      const unsigned long long pw2 = fma2(dx2, t2, mul2(mul2(pk2(Q2.x, Q2.y), dy2), dy2));
+      const unsigned long long e2 = add2(pw2, pk2(Q2.z, Q2.w));
+      float pw0, pw1, e0, e1;
+      upk2(pw2, pw0, pw1);
+      upk2(e2, e0, e1);
+      const float4 Q3 = sl.q3[j];
+      const float2 Q4 = *reinterpret_cast<const float2*>(sl.q4 + j);
+      {
+        const float alpha = fminf(kAlphaMax, ex2_approx(e0));
+        const bool valid = !done && (pw0 <= 0.f) && (alpha >= kAlphaMin);
+        const float next_T = T * (1.0f - alpha);
+        const bool stop = valid && (next_T <= kTMin);
+        const bool upd = valid && !stop;
+        done = done || stop;
+        const float wgt = upd ? alpha * T : 0.f;
+        prg = fma2(pk2(Q3.x, Q3.y), pk2(wgt, wgt), prg); pb = fmaf(Q4.x, wgt, pb);
+        T = upd ? next_T : T;
+        cur_idx = upd ? c0 + 2 * j : cur_idx;
+      }
+      {
+        const float alpha = fminf(kAlphaMax, ex2_approx(e1));
+        const bool valid = !done && (pw1 <= 0.f) && (alpha >= kAlphaMin);
+        const float next_T = T * (1.0f - alpha);
+        const bool stop = valid && (next_T <= kTMin);
+        const bool upd = valid && !stop;
+        done = done || stop;
+        const float wgt = upd ? alpha * T : 0.f;
+        prg = fma2(pk2(Q3.z, Q3.w), pk2(wgt, wgt), prg); pb = fmaf(Q4.y, wgt, pb);
+        T = upd ? next_T : T;
+        cur_idx = upd ? c0 + 2 * j + 1 : cur_idx;
+      }
     }
     if (__all_sync(0xffffffffu, done)) break;
   }
 
+  float pr, pg;
+  upk2(prg, pr, pg);
   float l1 = 0.f, l2 = 0.f;
   if (rg.inside) {
     const size_t pix = ((size_t)v * img_h + rg.py_i) * img_w + rg.px_i;
@@ -149,7 +201,7 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, 8) raster_rect_bwd_kernel(
     const int* __restrict__ final_idx, const float* __restrict__ v_out_img,
     const float* __restrict__ v_out_alpha, const float* __restrict__ out_img,
     const void* __restrict__ gt, int gt_u8, const float* __restrict__ v_loss, float* __restrict__ v_packed) {
-  __shared__ float4 sRec[kRectWarpsB][3][32];
+  __shared__ PairSlots sSlots[kRectWarpsB];
   __shared__ int sGid[kRectWarpsB][32];
   __shared__ float4 sVo[kRectWarpsB][32];
   __shared__ float2 sW[kRectWarpsB][kSlots * kSlotStride];
@@ -165,9 +217,7 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, 8) raster_rect_bwd_kernel(
   const int* ids = rect_ids + rect * cap;
   const float4* vp = packed + (size_t)v * n * 3;
   float* vgrad = v_packed + (size_t)v * n * 12;
-  float4* sA = sRec[warp][0];
-  float4* sB = sRec[warp][1];
-  float4* sC = sRec[warp][2];
+  PairSlots& sl = sSlots[warp];
   int* sG = sGid[warp];
 
   float T_final = 1.f, vo_r = 0.f, vo_g = 0.f, vo_b = 0.f, vo_a = 0.f;
@@ -211,18 +261,42 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, 8) raster_rect_bwd_kernel(
   float own_x = 0.f, own_y = 0.f;
   int own_g = 0;
 
-  // chunk c covers list positions [32c, 32c + 32); slot s of a chunk holds position 32c + s
+  // chunk c covers list positions [32c, 32c + 32); pair j of a chunk holds positions 32c + 2j, 32c + 2j + 1
+  const unsigned long long px2 = pk2(rg.px, rg.px), py2 = pk2(rg.py, rg.py);
+  const float4 nullA = make_float4(0.f, 0.f, 0.f, 0.f), nullB = make_float4(0.f, 0.f, 0.f, kNullLop);
   int c = warp_last >> 5;
-  float4 rA = make_float4(0.f, 0.f, 0.f, 0.f), rB = rA, rC = rA;
+  float4 rA = nullA, rB = nullB, rC = nullA;
   int rG = 0;
   if (32 * c + lane <= warp_last) {
     rG = __ldg(ids + 32 * c + lane);
     const float4* p = vp + (size_t)rG * 3;
     rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
   }
+  // one list entry, back to front: transmittance / accumulator update and parking of (w, fac)
+  auto entry = [&](int idx, float pw, float e, float cr, float cg, float cb, float gx, float gy, int slot) {
+    const float alpha_raw = ex2_approx(e);
+    const float alpha = fminf(kAlphaMax, alpha_raw);
+    const bool valid = (idx <= last) && (pw <= 0.f) && (alpha >= kAlphaMin);
+    if (!__any_sync(0xffffffffu, valid)) return;
+    const float ra = rcp_approx(1.0f - alpha);
+    T = valid ? T * ra : T;
+    const float fac = valid ? alpha * T : 0.f;
+    const float cdot = cr * vo_r + cg * vo_g + cb * vo_b;
+    const float v_alpha = T * cdot - ra * acc;
+    acc = fmaf(fac, cdot, acc);
+    // d alpha / d sigma = -alpha_raw where the 0.999 clamp is inactive, 0 where it is active
+    const float w = (valid && alpha_raw <= kAlphaMax) ? -alpha_raw * v_alpha : 0.f;
+    sW[warp][nslot * kSlotStride + lane] = make_float2(w, fac);
+    if ((lane & 15) == nslot) { own_x = gx; own_y = gy; own_g = sG[slot]; }
+    if (++nslot == kSlots) {
+      flush_slots<true>(sW[warp], sVo[warp], nullptr, kSlots, lane, own_x, own_y, own_g, rg.ox, rg.oy, vgrad);
+      nslot = 0;
+    }
+  };
   for (; c >= 0; --c) {
     __syncwarp();
-    sA[lane] = rA; sB[lane] = rB; sC[lane] = rC; sG[lane] = rG;
+    stage_pair_slots(sl, lane, rA, rB, rC);
+    sG[lane] = rG;
     __syncwarp();
     if (c > 0) {
       rG = __ldg(ids + 32 * (c - 1) + lane);
@@ -230,30 +304,20 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, 8) raster_rect_bwd_kernel(
       rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
     }
     const int top = min(31, warp_last - 32 * c);
-    for (int k = top; k >= 0; --k) {
-      const int idx = 32 * c + k;
-      const float4 A = sA[k], B = sB[k];
-      const float dx = A.x - rg.px, dy = A.y - rg.py;
-      const float pw = dx * fmaf(B.y, dy, B.x * dx) + B.z * dy * dy;
-      const float alpha_raw = ex2_approx(pw + B.w);
-      const float alpha = fminf(kAlphaMax, alpha_raw);
-      const bool valid = (idx <= last) && (pw <= 0.f) && (alpha >= kAlphaMin);
-      if (!__any_sync(0xffffffffu, valid)) continue;
-      const float4 C = sC[k];
-      const float ra = rcp_approx(1.0f - alpha);
-      T = valid ? T * ra : T;
-      const float fac = valid ? alpha * T : 0.f;
-      const float cdot = C.x * vo_r + C.y * vo_g + C.z * vo_b;
-      const float v_alpha = T * cdot - ra * acc;
-      acc = fmaf(fac, cdot, acc);
-      // d alpha / d sigma = -alpha_raw where the 0.999 clamp is inactive, 0 where it is active
-      const float w = (valid && alpha_raw <= kAlphaMax) ? -alpha_raw * v_alpha : 0.f;
-      sW[warp][nslot * kSlotStride + lane] = make_float2(w, fac);
-      if ((lane & 15) == nslot) { own_x = A.x; own_y = A.y; own_g = sG[k]; }
-      if (++nslot == kSlots) {
-        flush_slots<true>(sW[warp], sVo[warp], nullptr, kSlots, lane, own_x, own_y, own_g, rg.ox, rg.oy, vgrad);
-        nslot = 0;
-      }
+    for (int j = top >> 1; j >= 0; --j) {
+      const float4 Q0 = sl.q0[j], Q1 = sl.q1[j], Q2 = sl.q2[j];
+      const unsigned long long dx2 = sub2(pk2(Q0.x, Q0.y), px2), dy2 = sub2(pk2(Q0.z, Q0.w), py2);
+      const unsigned long long t2 = fma2(pk2(Q1.z, Q1.w), dy2, mul2(pk2(Q1.x, Q1.y), dx2));
+      const unsigned long long pw2 = fma2(dx2, t2, mul2(mul2(pk2(Q2.x, Q2.y), dy2), dy2));
+      const unsigned long long e2 = add2(pw2, pk2(Q2.z, Q2.w));
+      float pw0, pw1, e0, e1;
+      upk2(pw2, pw0, pw1);
+      upk2(e2, e0, e1);
+      const float4 Q3 = sl.q3[j];
+      const float2 Q4 = *reinterpret_cast<const float2*>(sl.q4 + j);
+      const int idx = 32 * c + 2 * j;
+      entry(idx + 1, pw1, e1, Q3.z, Q3.w, Q4.y, Q0.y, Q0.w, 2 * j + 1);
+      entry(idx, pw0, e0, Q3.x, Q3.y, Q4.x, Q0.x, Q0.z, 2 * j);
     }
   }
   if (nslot) flush_slots<true>(sW[warp], sVo[warp], nullptr, nslot, lane, own_x, own_y, own_g, rg.ox, rg.oy, vgrad);

@@ -66,6 +66,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJDIR, exist_ok=True)
     nvcc = _nvcc()
     extra = ["-Xptxas", "-v"] if verbose else []
+    extra += os.environ.get("SB_NVCC_DEFS", "").split()      # tuning experiments: -DNAME=value ...
 
     def compile_one(item):
         src, flags = item

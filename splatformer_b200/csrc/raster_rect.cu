@@ -194,7 +194,10 @@ __global__ void __launch_bounds__(kRectWarps * 32) raster_rect_fwd_kernel(
 // Gradient sums leave the warp through the transposed shared-memory reduction (raster_common.cuh:
 // flush_slots): 16 parked hits per flush, two red.global.add.v4.f32 + one scalar red per hit.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kRectWarpsB * 32, 8) raster_rect_bwd_kernel(
+#ifndef SB_RECT_BWD_MINB
+#define SB_RECT_BWD_MINB 7      // 72 registers: 64 forces address rematerialisation in the list walk
+#endif
+__global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rect_bwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ rect_ids,
     const int* __restrict__ rect_counts, int cap, const float* __restrict__ background, int tiles_x,
     int tiles_y, int img_w, int img_h, int clamped, const float* __restrict__ final_ts,

@@ -9,6 +9,7 @@ from splatformer_b200.api import (  # noqa: F401
 from splatformer_b200.sh import deg_from_sh, num_sh_bases  # noqa: F401
 from splatformer_b200.utils import (  # noqa: F401
     bin_and_sort_gaussians,
+    compute_cov2d_bounds,
     compute_cumulative_intersects,
     get_tile_bin_edges,
     map_gaussian_to_intersects,
@@ -18,4 +19,4 @@ from . import sh, utils  # noqa: F401
 __version__ = "0.1.11"
 __all__ = ["project_gaussians", "rasterize_gaussians", "spherical_harmonics", "num_sh_bases",
            "deg_from_sh", "bin_and_sort_gaussians", "compute_cumulative_intersects",
-           "get_tile_bin_edges", "map_gaussian_to_intersects", "__version__"]
+           "get_tile_bin_edges", "map_gaussian_to_intersects", "compute_cov2d_bounds", "__version__"]

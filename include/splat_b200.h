@@ -153,6 +153,13 @@ SB_API int sb_unpack_splat_grads(int count, const float* v_packed, const float* 
                           const float* opacity, float* v_xys, float* v_conics, float* v_colors,
                           float* v_opacity, sb_stream_t stream);
 
+/* ---- gsplat.utils.compute_cov2d_bounds [upstream gsplat/utils.py -> _C.compute_cov2d_bounds] ----
+ * (SURVEY.md 8b re-export list, 8f-4; never reached by SplatFormer.)  cov2d (count,3) = upper
+ * triangle (a, b, c) of the 2x2 screen covariance -> conics (count,3) = its inverse (c, -b, a)/det
+ * and radii (count,) int32 = ceil(3 sqrt(lambda_max)), discriminant floored at 0.1 as in the
+ * projection (A.2).  det == 0: conic 0, radius 0. */
+SB_API int sb_cov2d_bounds(int count, const float* cov2d, float* conics, int* radii, sb_stream_t stream);
+
 /* ---- a5-a9 for the fused path: fixed-capacity tile segments + per-tile depth sort ---------
  * Same per-tile order as sb_map_gaussian_to_intersects + sb_sort_pairs + sb_tile_bin_edges
  * (ascending depth bits, ties by ascending Gaussian id = the stable sort's emission order) without

@@ -273,6 +273,23 @@ def project_gaussians(means3d: Tensor, scales: Tensor, glob_scale: float, quats:
 # ----------------------------------------------------------------------------
 # A.4 intersections, sort, bins
 # ----------------------------------------------------------------------------
+def compute_cov2d_bounds(cov2d: Tensor) -> Tuple[Tensor, Tensor]:
+    """gsplat.utils.compute_cov2d_bounds [upstream]: conic = inverse of (a b; b c), radius =
+    ceil(3 sqrt(lambda_max)) with the discriminant floored at 0.1 (same lines as A.2)."""
+    a, b, c = cov2d[:, 0], cov2d[:, 1], cov2d[:, 2]
+    det = a * c - b * b
+    ok = det != 0
+    det_s = torch.where(ok, det, torch.ones_like(det))
+    inv = 1.0 / det_s
+    conic = torch.stack([c * inv, -b * inv, a * inv], dim=1)
+    mid = 0.5 * (a + c)
+    disc = _sqrt(torch.clamp(mid * mid - det_s, min=0.1))
+    radius = torch.ceil(3.0 * _sqrt(torch.maximum(mid + disc, mid - disc)))
+    conic = torch.where(ok[:, None], conic, torch.zeros_like(conic))
+    radius = torch.where(ok, radius, torch.zeros_like(radius))
+    return conic, radius.to(torch.int32)
+
+
 def compute_cumulative_intersects(num_tiles_hit: Tensor) -> Tuple[int, Tensor]:
     cum = torch.cumsum(num_tiles_hit, dim=0, dtype=torch.int32)
     return (int(cum[-1].item()) if cum.numel() else 0), cum
@@ -378,7 +395,8 @@ def rasterize_forward(xys: Tensor, conics: Tensor, colors: Tensor, opacity: Tens
     tiles_x = (img_width + block_width - 1) // block_width
     tiles_y = (img_height + block_width - 1) // block_width
     opac = opacity.reshape(-1)
-    img = torch.zeros(img_height, img_width, 3, dtype=dt)
+    channels = colors.shape[-1]                     # 3 for SplatFormer; N-channel variant = upstream nd_rasterize
+    img = torch.zeros(img_height, img_width, channels, dtype=dt)
     t_img = torch.ones(img_height, img_width, dtype=dt)
     idx_img = torch.zeros(img_height, img_width, dtype=torch.int32)
     margin_img = torch.full((img_height, img_width), 1e9, dtype=dt)
@@ -412,7 +430,8 @@ def rasterize_forward(xys: Tensor, conics: Tensor, colors: Tensor, opacity: Tens
             flat_pix.append(pix)
             flat_t.append(t_fin)
         index = torch.cat(flat_index)
-        img = img.reshape(-1, 3).index_put((index,), torch.cat(flat_pix)).reshape(img_height, img_width, 3)
+        img = img.reshape(-1, channels).index_put((index,), torch.cat(flat_pix)).reshape(
+            img_height, img_width, channels)
         t_img = t_img.reshape(-1).index_put((index,), torch.cat(flat_t)).reshape(img_height, img_width)
     out_img = img + t_img[:, :, None] * background.to(dt)[None, None, :]
     return out_img, t_img, idx_img, margin_img

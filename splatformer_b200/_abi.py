@@ -40,6 +40,7 @@ SIGNATURES = {
     "sb_rasterize_fwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, I, P, I, P, P]),
     "sb_rasterize_bwd": (I, [I, I, P, P, P, P, I, I, I, P, P, P, P, P, I, P, I, P, P, P]),
     "sb_unpack_splat_grads": (I, [I, P, P, P, P, P, P, P, P]),
+    "sb_cov2d_bounds": (I, [I, P, P, P, P]),
     "sb_views_project_fwd": (I, [I, I, P, P, F, P, P, P, P, I, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P,
                                  P, P, I, P]),
     "sb_tile_sort_capacity": (I, []),

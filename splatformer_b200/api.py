@@ -181,23 +181,32 @@ class _RasterizeGaussians(Function):
         (_, _, _, gaussian_ids_sorted, tile_bins) = utils.bin_and_sort_gaussians(
             n, num_intersects, xys, _f(depths), _f(radii), cum_tiles_hit, (tiles_x, tiles_y, 1),
             block_width)
-        packed = _pack(xys, conics, colors, opacity)
         background = _f(background.to(F32))
-        out_img = torch.empty(img_height, img_width, 3, dtype=F32, device=dev)
         final_ts = torch.empty(img_height, img_width, dtype=F32, device=dev)
         final_idx = torch.empty(img_height, img_width, dtype=I32, device=dev)
         out_alpha = torch.empty(img_height, img_width, dtype=F32, device=dev) if return_alpha else None
-        _abi.check(lib.sb_rasterize_fwd(
-            1, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
-            _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
-            img_width, block_width, None, _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
-            _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"), 0, None, 0, None,
-            _abi.stream()), "sb_rasterize_fwd")
+        # The kernels composite three channels per pass; other channel counts (upstream's nd_rasterize,
+        # SURVEY.md 8f-4) run ceil(C/3) passes over the same sorted lists, zero-padding the last group.
+        groups = _channel_groups(channels)
+        parts, packs = [], []
+        for lo, width in groups:
+            cols_g, bg_g = _group3(colors, lo, width), _group3(background, lo, width)
+            packed = _pack(xys, conics, cols_g, opacity)
+            img_g = torch.empty(img_height, img_width, 3, dtype=F32, device=dev)
+            _abi.check(lib.sb_rasterize_fwd(
+                1, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
+                _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(bg_g, F32, "background"), img_height,
+                img_width, block_width, None, _abi.ptr(img_g, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
+                _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"), 0, None, 0, None,
+                _abi.stream()), "sb_rasterize_fwd")
+            parts.append(img_g if width == 3 else img_g[..., :width])
+            packs.append(packed)
+        out_img = parts[0] if len(parts) == 1 else torch.cat(parts, dim=-1)
         ctx.empty = False
         ctx.num_intersects = num_intersects
-        ctx.meta = (n, img_height, img_width, block_width)
-        ctx.save_for_backward(packed, gaussian_ids_sorted, tile_bins, background, final_ts, final_idx, conics,
-                              opacity)
+        ctx.meta = (n, img_height, img_width, block_width, channels)
+        ctx.save_for_backward(gaussian_ids_sorted, tile_bins, background, final_ts, final_idx, conics, opacity,
+                              *packs)
         ctx.set_materialize_grads(False)
         return (out_img, out_alpha) if return_alpha else out_img
 
@@ -207,30 +216,55 @@ class _RasterizeGaussians(Function):
         if ctx.empty or (v_out_img is None and v_out_alpha is None):
             return none12
         lib = _abi.load()
-        (packed, gaussian_ids_sorted, tile_bins, background, final_ts, final_idx, conics,
-         opacity) = ctx.saved_tensors
-        n, img_height, img_width, block_width = ctx.meta
-        dev = packed.device
-        v_out_img = torch.zeros(img_height, img_width, 3, dtype=F32, device=dev) if v_out_img is None \
+        (gaussian_ids_sorted, tile_bins, background, final_ts, final_idx, conics, opacity,
+         *packs) = ctx.saved_tensors
+        n, img_height, img_width, block_width, channels = ctx.meta
+        dev = conics.device
+        v_out_img = torch.zeros(img_height, img_width, channels, dtype=F32, device=dev) if v_out_img is None \
             else _f(v_out_img)
         v_out_alpha = None if v_out_alpha is None else _f(v_out_alpha)
-        v_packed = torch.zeros(n, 12, dtype=F32, device=dev)
-        _abi.check(lib.sb_rasterize_bwd(
-            1, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
-            _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
-            img_width, block_width, _abi.ptr(final_ts, F32, "final_Ts"), _abi.ptr(final_idx, I32, "final_idx"),
-            _abi.ptr(v_out_img, F32, "v_out_img"), _abi.ptr(v_out_alpha, F32, "v_out_alpha"), None, 0, None, 0, None,
-            _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_bwd")
-        v_xys = torch.empty(n, 2, dtype=F32, device=dev)
-        v_conics = torch.empty(n, 3, dtype=F32, device=dev)
-        v_colors = torch.empty(n, 3, dtype=F32, device=dev)
-        v_opacity = torch.empty(n, 1, dtype=F32, device=dev)
-        _abi.check(lib.sb_unpack_splat_grads(
-            n, _abi.ptr(v_packed, F32, "v_packed"), _abi.ptr(conics, F32, "conics"),
-            _abi.ptr(opacity, F32, "opacity"), _abi.ptr(v_xys, F32, "v_xys"),
-            _abi.ptr(v_conics, F32, "v_conics"), _abi.ptr(v_colors, F32, "v_colors"),
-            _abi.ptr(v_opacity, F32, "v_opacity"), _abi.stream()), "sb_unpack_splat_grads")
+        v_xys = v_conics = v_opacity = None
+        v_color_parts = []
+        for gi, (lo, width) in enumerate(_channel_groups(channels)):
+            v_img_g, bg_g = _group3(v_out_img, lo, width), _group3(background, lo, width)
+            v_packed = torch.zeros(n, 12, dtype=F32, device=dev)
+            # d/d alpha enters once: with the first group
+            _abi.check(lib.sb_rasterize_bwd(
+                1, n, _abi.ptr(packs[gi], F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
+                _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(bg_g, F32, "background"), img_height,
+                img_width, block_width, _abi.ptr(final_ts, F32, "final_Ts"), _abi.ptr(final_idx, I32, "final_idx"),
+                _abi.ptr(v_img_g, F32, "v_out_img"), _abi.ptr(v_out_alpha if gi == 0 else None, F32, "v_out_alpha"),
+                None, 0, None, 0, None, _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_bwd")
+            g_xys = torch.empty(n, 2, dtype=F32, device=dev)
+            g_conics = torch.empty(n, 3, dtype=F32, device=dev)
+            g_colors = torch.empty(n, 3, dtype=F32, device=dev)
+            g_opacity = torch.empty(n, 1, dtype=F32, device=dev)
+            _abi.check(lib.sb_unpack_splat_grads(
+                n, _abi.ptr(v_packed, F32, "v_packed"), _abi.ptr(conics, F32, "conics"),
+                _abi.ptr(opacity, F32, "opacity"), _abi.ptr(g_xys, F32, "v_xys"),
+                _abi.ptr(g_conics, F32, "v_conics"), _abi.ptr(g_colors, F32, "v_colors"),
+                _abi.ptr(g_opacity, F32, "v_opacity"), _abi.stream()), "sb_unpack_splat_grads")
+            v_xys = g_xys if v_xys is None else v_xys + g_xys
+            v_conics = g_conics if v_conics is None else v_conics + g_conics
+            v_opacity = g_opacity if v_opacity is None else v_opacity + g_opacity
+            v_color_parts.append(g_colors if width == 3 else g_colors[:, :width])
+        v_colors = v_color_parts[0] if len(v_color_parts) == 1 else torch.cat(v_color_parts, dim=-1)
         return (v_xys, None, None, v_conics, None, v_colors, v_opacity, None, None, None, None, None)
+
+
+def _channel_groups(channels: int):
+    """[(first channel, width <= 3)] covering `channels`."""
+    return [(lo, min(3, channels - lo)) for lo in range(0, channels, 3)]
+
+
+def _group3(t: Tensor, lo: int, width: int) -> Tensor:
+    """Channels [lo, lo+width) of the last dimension as a contiguous 3-channel tensor (zero-padded)."""
+    if lo == 0 and width == 3 and t.shape[-1] == 3:
+        return t
+    part = t[..., lo:lo + width]
+    if width < 3:
+        part = torch.nn.functional.pad(part, (0, 3 - width))
+    return _f(part)
 
 
 def rasterize_gaussians(xys: Tensor, depths: Tensor, radii: Tensor, conics: Tensor,
@@ -238,7 +272,9 @@ def rasterize_gaussians(xys: Tensor, depths: Tensor, radii: Tensor, conics: Tens
                         img_width: int, block_width: int, background: Optional[Tensor] = None,
                         return_alpha: Optional[bool] = False):
     """Rasterise 2D Gaussians: sort by (tile, depth), composite front to back per 16x16 tile.
-    Returns out_img (H,W,3) [and out_alpha (H,W) = 1 - final transmittance if return_alpha]."""
+    Returns out_img (H,W,C) [and out_alpha (H,W) = 1 - final transmittance if return_alpha].
+    C = 3 is what SplatFormer uses (/root/reference/utils/gs_utils.py:65,78); any other channel count
+    (upstream's nd_rasterize path) is composited three channels per pass over the same sorted lists."""
     assert block_width > 1 and block_width <= 16, "block_width must be between 2 and 16"
     if colors.dtype == torch.uint8:
         colors = colors.float() / 255
@@ -251,10 +287,8 @@ def rasterize_gaussians(xys: Tensor, depths: Tensor, radii: Tensor, conics: Tens
         raise ValueError("xys must have dimensions (N, 2)")
     if colors.ndimension() != 2:
         raise ValueError("colors must have dimensions (N, D)")
-    if colors.shape[-1] != 3:
-        raise NotImplementedError(
-            "only 3-channel colours are implemented (SplatFormer never uses another count, "
-            "/root/reference/utils/gs_utils.py:65,78); the N-channel variant is a 'next' row")
+    if colors.shape[-1] < 1:
+        raise ValueError("colors must have at least one channel")
     res = _RasterizeGaussians.apply(xys, depths, radii, conics, num_tiles_hit, colors,
                                     opacity.reshape(-1, 1), img_height, img_width, block_width,
                                     background, bool(return_alpha))

@@ -38,7 +38,38 @@ __global__ void __launch_bounds__(256) unpack_grads_kernel(int count, const floa
   v_colors[3 * i] = b.z; v_colors[3 * i + 1] = b.w; v_colors[3 * i + 2] = c.x;
 }
 
+// gsplat.utils.compute_cov2d_bounds (upstream _C.compute_cov2d_bounds): conic = inverse of the 2x2
+// covariance (a b; b c), radius = ceil(3 sqrt(largest eigenvalue)) with the discriminant floored at
+// 0.1 as in the projection kernel; a singular covariance gives conic 0, radius 0.
+__global__ void __launch_bounds__(256) cov2d_bounds_kernel(int count, const float* __restrict__ cov2d,
+                                                           float* __restrict__ conics, int* __restrict__ radii) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= count) return;
+  const float a = __ldg(cov2d + 3 * i), b = __ldg(cov2d + 3 * i + 1), c = __ldg(cov2d + 3 * i + 2);
+  // one IEEE rounding per operation, no FMA contraction: same bits as the oracle's float32 chain
+  const float det = __fsub_rn(__fmul_rn(a, c), __fmul_rn(b, b));
+  float ka = 0.f, kb = 0.f, kc = 0.f;
+  int radius = 0;
+  if (det != 0.f) {
+    const float inv = __fdiv_rn(1.0f, det);
+    ka = __fmul_rn(c, inv); kb = __fmul_rn(-b, inv); kc = __fmul_rn(a, inv);
+    const float mid = __fmul_rn(0.5f, __fadd_rn(a, c));
+    const float disc = __fsqrt_rn(fmaxf(0.1f, __fsub_rn(__fmul_rn(mid, mid), det)));
+    const float r = ceilf(__fmul_rn(3.0f, __fsqrt_rn(fmaxf(__fadd_rn(mid, disc), __fsub_rn(mid, disc)))));
+    radius = (r >= 0.f && r <= 1073741824.0f) ? (int)r : 0;
+  }
+  conics[3 * i] = ka; conics[3 * i + 1] = kb; conics[3 * i + 2] = kc;
+  radii[i] = radius;
+}
+
 }  // namespace sb
+
+extern "C" int sb_cov2d_bounds(int count, const float* cov2d, float* conics, int* radii, sb_stream_t stream) {
+  if (count < 0) return SB_ERR_BAD_ARG;
+  if (count == 0) return 0;
+  sb::cov2d_bounds_kernel<<<sb::ceil_div(count, 256), 256, 0, (cudaStream_t)stream>>>(count, cov2d, conics, radii);
+  SB_RETURN_LAST();
+}
 
 extern "C" int sb_abi_version(void) { return SB_ABI_VERSION; }
 

@@ -15,6 +15,24 @@ def _scratch(nbytes: int, device) -> Tensor:
     return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)
 
 
+def compute_cov2d_bounds(cov2d: Tensor) -> Tuple[Tensor, Tensor]:
+    """gsplat.utils.compute_cov2d_bounds: (N,3) upper triangles of 2x2 covariances -> conics (N,3)
+    (the inverses) and radii (N,) int32 = ceil(3 sqrt(largest eigenvalue)).  Not differentiable,
+    as upstream."""
+    if cov2d.shape[-1] != 3:
+        raise ValueError("cov2d must have shape (N, 3)")
+    if not cov2d.is_cuda:
+        raise RuntimeError("compute_cov2d_bounds needs a CUDA tensor (there is no CPU path)")
+    lib = _abi.load()
+    flat = cov2d.detach().to(torch.float32).contiguous().view(-1, 3)
+    n = flat.shape[0]
+    conics = torch.empty(n, 3, dtype=torch.float32, device=flat.device)
+    radii = torch.empty(n, dtype=torch.int32, device=flat.device)
+    _abi.check(lib.sb_cov2d_bounds(n, _abi.ptr(flat, torch.float32, "cov2d"), _abi.ptr(conics, torch.float32, "conics"),
+                                   _abi.ptr(radii, torch.int32, "radii"), _abi.stream()), "sb_cov2d_bounds")
+    return conics, radii
+
+
 def compute_cumulative_intersects(num_tiles_hit: Tensor, sync: bool = True) -> Tuple[int, Tensor]:
     """Inclusive int32 prefix sum of the per-Gaussian tile counts and its last element.
     The `.item()` is the one host synchronisation upstream has here as well (sync=False skips it and

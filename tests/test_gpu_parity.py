@@ -221,3 +221,56 @@ def test_full_view_pipeline_matches_oracle(cuda, sb_lib):
     assert abs(float(loss) - float(loss_ref)) < 1e-5
     for name in gs:
         H.assert_grad_close(raw[name].grad, raw_ref[name].grad, name, rtol=5e-3)
+
+
+@pytest.mark.parametrize("channels", [1, 2, 4, 7])
+def test_rasterize_n_channels(cuda, sb_lib, channels):
+    """Colour counts other than 3 (upstream's nd_rasterize path): image, alpha and all
+    four gradients against the float64 oracle."""
+    gs, cams = _scene(1500, 0, (88, 72), 0.3, seed=5)
+    k = H.cam_scalars(cams)
+    inp = H.view_inputs(gs, cams, 1)
+    with torch.no_grad():
+        xys, depths, radii, conics, comp, tiles, cov3d = R.project_gaussians(
+            inp["means"], inp["scales"], 1, inp["quats"], inp["viewmat"], k["fx"], k["fy"], k["cx"], k["cy"],
+            k["H"], k["W"], 16)
+    gen = torch.Generator().manual_seed(channels)
+    colors = torch.rand(xys.shape[0], channels, generator=gen)
+    bg = torch.rand(channels, generator=gen)
+    ref_leaves = [t.double().clone().requires_grad_() for t in (xys, conics, colors, inp["opacities"])]
+    img_ref, alpha_ref, aux = R.rasterize_gaussians(
+        ref_leaves[0], depths, radii, ref_leaves[1], tiles, ref_leaves[2], ref_leaves[3], k["H"], k["W"], 16,
+        background=bg.double(), return_alpha=True, return_aux=True)
+    leaves = [t.to(cuda).clone().requires_grad_() for t in (xys, conics, colors, inp["opacities"])]
+    img, alpha = gsplat.rasterize_gaussians(leaves[0], depths.to(cuda), radii.to(cuda), leaves[1], tiles.to(cuda),
+                                            leaves[2], leaves[3], k["H"], k["W"], 16, background=bg.to(cuda),
+                                            return_alpha=True)
+    assert img.shape == (k["H"], k["W"], channels) and alpha.shape == (k["H"], k["W"])
+    solid = aux["margin"] > H.FRAGILE_MARGIN
+    assert float((img.cpu().double() - img_ref.detach()).abs().amax(-1)[solid].max()) <= H.IMG_ATOL
+    assert float((alpha.cpu().double() - alpha_ref.detach()).abs()[solid].max()) <= H.IMG_ATOL
+    v_img = torch.randn(img_ref.shape, dtype=torch.float64, generator=gen) * solid[..., None]
+    v_alpha = torch.randn(alpha_ref.shape, dtype=torch.float64, generator=gen) * solid
+    ((img_ref * v_img).sum() + (alpha_ref * v_alpha).sum()).backward()
+    ((img * v_img.float().to(cuda)).sum() + (alpha * v_alpha.float().to(cuda)).sum()).backward()
+    for nm, a, b in zip(("v_xys", "v_conics", "v_colors", "v_opacity"), leaves, ref_leaves):
+        H.assert_grad_close(a.grad, b.grad, nm)
+    with pytest.raises(AssertionError):
+        gsplat.rasterize_gaussians(leaves[0], depths.to(cuda), radii.to(cuda), leaves[1], tiles.to(cuda), leaves[2],
+                                   leaves[3], k["H"], k["W"], 16, background=torch.ones(channels + 1, device=cuda))
+
+
+def test_compute_cov2d_bounds(cuda, sb_lib):
+    gen = torch.Generator().manual_seed(0)
+    l = torch.randn(4000, 2, 2, generator=gen) * torch.logspace(-1, 1.5, 4000)[:, None, None]
+    cov = l @ l.transpose(1, 2) + 0.3 * torch.eye(2)
+    cov2d = torch.stack([cov[:, 0, 0], cov[:, 0, 1], cov[:, 1, 1]], dim=1).contiguous()
+    cov2d[:5] = torch.tensor([[1.0, 1.0, 1.0], [0.0, 0.0, 0.0], [4.0, 2.0, 1.0], [1.0, 0.0, 1.0], [2.0, 0.0, 0.5]])
+    conic_ref, radius_ref = R.compute_cov2d_bounds(cov2d)
+    conic, radius = gsplat.utils.compute_cov2d_bounds(cov2d.to(cuda))
+    assert radius.dtype == torch.int32 and conic.shape == (4000, 3)
+    assert bool((radius[:3].cpu() == 0).all()) and bool((conic[:3] == 0).all())     # singular: det == 0
+    assert int(radius[3]) == 4 and torch.allclose(conic[3].cpu(), torch.tensor([1.0, 0.0, 1.0]))
+    # the kernel rounds once per operation like the oracle's float32 chain: identical bits
+    assert torch.equal(conic.cpu(), conic_ref)
+    assert torch.equal(radius.cpu(), radius_ref)

@@ -8,6 +8,8 @@ import pytest
 import torch
 
 from oracle import ref_torch as R
+from splatformer_b200 import synth
+import helpers as H
 
 
 def _identity_view():
@@ -220,3 +222,31 @@ def test_tile_bins_and_keys_small():
     assert int(keys[1] & 0xFFFFFFFF) == one
     assert gids_s.tolist() == [1, 0, 1, 2, 1, 1]                 # tile 0: depth 1 then 3; tile 1: 1 then 2
     assert bins.tolist() == [[0, 2], [2, 4], [4, 5], [5, 6]]
+
+
+def test_cov2d_bounds_known_answers():
+    """compute_cov2d_bounds: identity covariance -> conic (1,0,1); lambda_max = 1 + sqrt(0.1) (the
+    discriminant floor), radius = ceil(3 sqrt(1.316)) = 4; diag(4, 1): conic (0.25, 0, 1), radius
+    ceil(3*2) = 6; singular -> zeros."""
+    cov = torch.tensor([[1.0, 0.0, 1.0], [4.0, 0.0, 1.0], [1.0, 1.0, 1.0]])
+    conic, radius = R.compute_cov2d_bounds(cov)
+    assert torch.allclose(conic, torch.tensor([[1.0, 0.0, 1.0], [0.25, 0.0, 1.0], [0.0, 0.0, 0.0]]))
+    assert radius.tolist() == [4, 6, 0] and radius.dtype == torch.int32
+
+
+def test_oracle_rasterizes_any_channel_count():
+    """The first three channels of a 5-channel render equal the 3-channel render of the same splats."""
+    gs = synth.shell_scene(300, 0, seed=3, scale_mult=0.6)
+    cams = synth.orbit_cameras(1, 48, 40)
+    k = H.cam_scalars(cams)
+    inp = H.view_inputs(gs, cams, 0)
+    p = R.project_gaussians(inp["means"], inp["scales"], 1, inp["quats"], inp["viewmat"], k["fx"], k["fy"], k["cx"],
+                            k["cy"], k["H"], k["W"], 16)
+    cols = torch.rand(300, 5, generator=torch.Generator().manual_seed(1))
+    bg = torch.tensor([0.1, 0.2, 0.3, 0.4, 0.5])
+    img5, a5 = R.rasterize_gaussians(p[0], p[1], p[2], p[3], p[5], cols, inp["opacities"], k["H"], k["W"], 16,
+                                     background=bg, return_alpha=True)
+    img3, a3 = R.rasterize_gaussians(p[0], p[1], p[2], p[3], p[5], cols[:, :3].contiguous(), inp["opacities"],
+                                     k["H"], k["W"], 16, background=bg[:3], return_alpha=True)
+    assert img5.shape == (40, 48, 5) and torch.equal(a5, a3)
+    assert torch.allclose(img5[..., :3], img3, atol=1e-6)

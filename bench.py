@@ -219,6 +219,8 @@ def main() -> None:
     ap.add_argument("--cpu-views", type=int, default=3, help="views of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--wrapper-steps", type=int, default=5,
+                    help="timed steps of the unmodified per-view wrapper path (0 = skip)")
     ap.add_argument("--ref-views", type=int, default=2)
     ap.add_argument("--steps-ref", type=int, default=None)
     ap.add_argument("--warmup-ref", type=int, default=None)
@@ -348,6 +350,22 @@ def main() -> None:
         for i in range(3):
             step_e2e(i)
         e2e_ms, _, _, _ = timed(step_e2e, args.steps)
+    # ---- the unmodified wrapper path: the reference's per-view Python loop on the
+    # gsplat-compatible API -- what SplatFormer runs when only `import gsplat` is redirected here
+    wrapper_ms = None
+    if args.wrapper_steps > 0 and world == 1:
+        def step_wrapper(i):
+            raw, cams, gt = resident[i % NSCENE]
+            for p in raw.values():
+                p.grad = None
+            rgbs, _ = gs_utils.per_view_multiimgs(raw, cams)
+            loss = 0.0
+            for rgb, g in zip(rgbs, gt):                     # train.py:274-275
+                loss = loss + (rgb - g.float() / 255.0).abs().mean()
+            (loss * inv_views).backward()
+        for i in range(2):
+            step_wrapper(i)
+        wrapper_ms, wrapper_launches, _, _ = timed(step_wrapper, args.wrapper_steps)
     clocks = sampler.stop() if sampler else None
 
     if rank == 0:
@@ -412,6 +430,13 @@ def main() -> None:
             line["e2e"] = {"value": pix_step / (e2e_step * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_step,
                            "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4,
                            "api": "splatformer_b200.gs_utils.render_l1_loss(gs_params, cameras, images) + backward"}
+        if wrapper_ms is not None:
+            w_step = wrapper_ms / args.wrapper_steps
+            line["wrapper_path"] = {"value": pix_step / (w_step * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": w_step,
+                                    "steps": args.wrapper_steps, "abi_launches_per_step": wrapper_launches / args.wrapper_steps,
+                                    "api": "splatformer_b200.gs_utils.per_view_multiimgs = the loop of "
+                                           "utils/gs_utils.py:20-114 on gsplat.spherical_harmonics / project_gaussians / "
+                                           "rasterize_gaussians, + torch L1 loss + backward"}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args.cpu_views)
         print(json.dumps(line), flush=True)

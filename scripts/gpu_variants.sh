@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 for DEFS in "$@"; do
   SB_NVCC_DEFS="$DEFS" python -m splatformer_b200.build --force > /dev/null 2> gpurun_out/variant_build.err || { echo "build failed: $DEFS"; tail -5 gpurun_out/variant_build.err; continue; }
-  python bench.py --steps 40 --warmup 5 --no-cpu-baseline --no-e2e > gpurun_out/variant.json 2>/dev/null
+  python bench.py --steps 40 --warmup 5 --no-cpu-baseline --no-e2e --wrapper-steps 0 > gpurun_out/variant.json 2>/dev/null
   python - "$DEFS" <<PY
 import json, sys
 d = json.loads(open("gpurun_out/variant.json").read().strip().splitlines()[-1])

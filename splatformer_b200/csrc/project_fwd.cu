@@ -135,12 +135,25 @@ __global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
           }
         }
       } else {
-        for (int ty = o.min_y; ty < o.max_y; ++ty)
-          for (int tx = o.min_x; tx < o.max_x; ++tx) {
-            const size_t t = t0 + (size_t)ty * tiles_x + tx;
-            const int p1 = atomicAdd(tile_counts + t, 1);
-            if (p1 < tile_cap) tile_keys[t * tile_cap + p1] = key;
+        // many tiles: claim the slots eight at a time so that the atomics' round trips overlap instead
+        // of queueing behind each other (a 1M-Gaussian room scene averages 47 tiles per Gaussian)
+        const int total = nx * (o.max_y - o.min_y);
+        for (int b0 = 0; b0 < total; b0 += 8) {
+          size_t tb[8];
+          int pb[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int e = b0 + k;
+            if (e < total) {
+              const int ky = e / nx, kx = e - ky * nx;
+              tb[k] = t0 + (size_t)(o.min_y + ky) * tiles_x + (o.min_x + kx);
+              pb[k] = atomicAdd(tile_counts + tb[k], 1);
+            }
           }
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (b0 + k < total && pb[k] < tile_cap) tile_keys[tb[k] * tile_cap + pb[k]] = key;
+        }
       }
     }
     float r, gg, b;

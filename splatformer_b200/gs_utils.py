@@ -137,3 +137,53 @@ def rasterize_gaussians_to_singleimg(gs_params: Dict[str, Tensor], camera_to_wor
     rgb, alpha = render_scene(gs_params, camera_to_world[None], cx, cy, fx, fy, width, height,
                               background_color)
     return rgb[0], alpha[0]
+
+
+# ------------------------------------------------------------------------------------------------
+# Drop-in level 1: the reference's own per-view wrapper logic on the gsplat-compatible API.
+# This is what SplatFormer runs when only `import gsplat` is redirected to this repository
+# (three API calls and about nine host synchronisations per view); bench.py times it next to the
+# fused path ("wrapper_path"), and the tests use it to tie the fused path to the per-view API.
+# ------------------------------------------------------------------------------------------------
+def per_view_singleimg(gs_params: Dict[str, Tensor], camera_to_world: Tensor, cx, cy, fx, fy, width, height,
+                       background_color: Tensor, **kwargs) -> Tuple[Tensor, Tensor]:
+    """One view through spherical_harmonics / project_gaussians / rasterize_gaussians with the
+    conventions of /root/reference/utils/gs_utils.py:29-114."""
+    from . import api
+    gp = {k: (v.float() if v.dtype == torch.half else v) for k, v in gs_params.items()}
+    viewmats, campos = viewmats_from_c2w(camera_to_world[None])                 # :32-42
+    means = gp["means"]
+    scales = torch.exp(gp["scales"])                                            # :45
+    quats = gp["quats"] / torch.norm(gp["quats"], dim=-1, keepdim=True)         # :46
+    if "opacities" in gp:                                                       # :53-58
+        opacities = torch.sigmoid(gp["opacities"])
+    elif "opacities_sigmoid" in gp:
+        opacities = gp["opacities_sigmoid"]
+    else:
+        raise ValueError("No opacities found in gs_params")
+    coeffs = gp["features_dc"].unsqueeze(1)
+    if "features_rest" in gp:
+        coeffs = torch.cat([coeffs, gp["features_rest"]], dim=1)                # :59-62
+    degree = int(math.sqrt(coeffs.shape[1]) - 1)
+    if degree == 0:
+        rgbs = torch.sigmoid(coeffs[:, 0, :])                                   # :65
+    else:
+        dirs = means.detach() - campos[0]
+        dirs = dirs / dirs.norm(dim=-1, keepdim=True)
+        rgbs = torch.clamp(api.spherical_harmonics(degree, dirs, coeffs) + 0.5, min=0.0)   # :78-79
+    h, w = int(_scalar(height)), int(_scalar(width))                            # host syncs, as upstream (:80)
+    xys, depths, radii, conics, _comp, num_tiles_hit, _cov3d = api.project_gaussians(
+        means, scales, 1, quats, viewmats[0], _scalar(fx), _scalar(fy), _scalar(cx), _scalar(cy), h, w, BLOCK_WIDTH)
+    rgb, alpha = api.rasterize_gaussians(xys, depths, radii, conics, num_tiles_hit, rgbs, opacities, h, w,
+                                         BLOCK_WIDTH, background=background_color, return_alpha=True)
+    return torch.clamp(rgb, max=1.0), alpha.unsqueeze(-1)                       # :111-112
+
+
+def per_view_multiimgs(gs_params: Dict[str, Tensor], cameras: Dict[str, Tensor]) -> Tuple[List[Tensor], List[Tensor]]:
+    """The reference's Python loop over the views (/root/reference/utils/gs_utils.py:20-27)."""
+    rgbs, alphas = [], []
+    for c2w in cameras["camera_to_worlds"]:
+        rgb, alpha = per_view_singleimg(gs_params, c2w, **cameras)
+        rgbs.append(rgb)
+        alphas.append(alpha)
+    return rgbs, alphas

@@ -216,3 +216,23 @@ def test_fused_tile_overflow_falls_back_to_global_sort(cuda, sb_lib, monkeypatch
     l1_a.sum().backward(); l1_b.sum().backward()
     for name in gs:
         H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name)
+
+
+def test_per_view_wrapper_matches_fused_path(cuda, sb_lib):
+    """gs_utils.per_view_multiimgs (the reference's loop on the three gsplat-compatible calls, what
+    bench.py reports as wrapper_path) against rasterize_gaussians_to_multiimgs (fused)."""
+    gs = synth.shell_scene(2000, 2, seed=14, scale_mult=0.3)
+    cams = {k_: v.to(cuda) for k_, v in synth.orbit_cameras(3, 120, 88, background=(0.2, 0.3, 0.1)).items()}
+    gt = synth.target_images(3, 88, 120, seed=9).to(cuda)
+    raw_a = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    raw_b = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    rgbs_a, alphas_a = gs_utils.rasterize_gaussians_to_multiimgs(raw_a, cams)
+    rgbs_b, alphas_b = gs_utils.per_view_multiimgs(raw_b, cams)
+    for v in range(3):
+        assert rgbs_b[v].shape == (88, 120, 3) and alphas_b[v].shape == (88, 120, 1)
+        assert float((rgbs_a[v] - rgbs_b[v]).abs().max()) <= 1e-5
+        assert float((alphas_a[v] - alphas_b[v]).abs().max()) <= 1e-5
+    sum((r - g).abs().mean() for r, g in zip(rgbs_a, gt)).backward()
+    sum((r - g).abs().mean() for r, g in zip(rgbs_b, gt)).backward()
+    for name in gs:
+        H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name)

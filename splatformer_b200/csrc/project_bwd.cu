@@ -111,7 +111,10 @@ __device__ __forceinline__ float sum_view_lanes(float x) {
 }
 
 template <int DEG>
-__global__ void __launch_bounds__(kViewsBwdBlock, 4) views_project_bwd_kernel(
+#ifndef SB_PROJ_BWD_MINB
+#define SB_PROJ_BWD_MINB 4
+#endif
+__global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_project_bwd_kernel(
     int num_views, int n, const float* __restrict__ means, const float* __restrict__ scales, float glob,
     const float* __restrict__ quats, int flags, CamSrc cams, const float* __restrict__ campos, int img_h,
     int img_w, int bw, float clip, int k3_store, const float4* __restrict__ packed,

@@ -64,7 +64,10 @@ __device__ __forceinline__ void stage_pair_slots(PairSlots& sl, int lane, const 
   reinterpret_cast<float*>(sl.q4 + j)[h] = rC.z;
 }
 
-__global__ void __launch_bounds__(kRectWarps * 32) raster_rect_fwd_kernel(
+#ifndef SB_RECT_FWD_MINB
+#define SB_RECT_FWD_MINB 4      // 64 registers, 4 CTAs/SM: measured best (3 CTAs at 80 registers: +8 %)
+#endif
+__global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect_fwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ rect_ids,
     const int* __restrict__ rect_counts, int cap, const float* __restrict__ background, int tiles_x,
     int tiles_y, int img_w, int img_h, const int* __restrict__ view_has_isects,
@@ -105,7 +108,12 @@ __global__ void __launch_bounds__(kRectWarps * 32) raster_rect_fwd_kernel(
       rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
     }
     const int npairs = (min(32, count - c0) + 1) >> 1;
-#pragma unroll 4
+#ifndef SB_RECT_FWD_UNROLL
+#define SB_RECT_FWD_UNROLL 4
+#endif
+#define SB_PRAGMA_(x) _Pragma(#x)
+#define SB_UNROLL_(n) SB_PRAGMA_(unroll n)
+    SB_UNROLL_(SB_RECT_FWD_UNROLL)
     for (int j = 0; j < npairs; ++j) {
       const float4 Q0 = sl.q0[j], Q1 = sl.q1[j], Q2 = sl.q2[j];
       // both entries of the pair at once; every half rounds exactly like the scalar expression

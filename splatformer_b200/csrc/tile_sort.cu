@@ -49,7 +49,10 @@ __device__ __forceinline__ void bitonic_sort_smem(unsigned long long* s, int len
 
 // dynamic shared memory: keys[cap] (8 B each) then ends[cap] (4 B each); cap = segment capacity (power of two)
 // totals: [0] += intersections, [1] = 1 if some tile overflowed its segment.
-__global__ void __launch_bounds__(kSortBlock) sort_tiles_kernel(int cap, int tiles_per_view,
+#ifndef SB_SORT_MINB
+#define SB_SORT_MINB 6
+#endif
+__global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(int cap, int tiles_per_view,
                                                                 const int* __restrict__ counts,
                                                                 const unsigned long long* __restrict__ keys,
                                                                 int* __restrict__ gids_sorted, int2* __restrict__ bins,

@@ -95,6 +95,17 @@ __global__ void __launch_bounds__(NW * 32) raster_bwd_kernel(
   const float oy = (float)(tile_y * bw + (warp_t >> 1) * 4) + 0.5f;
   const float bg_dot = __ldg(background) * vo_r + __ldg(background + 1) * vo_g + __ldg(background + 2) * vo_b;
   const int warp_final = __reduce_max_sync(0xffffffffu, bin_final);
+  // The walk starts at the last Gaussian any pixel of this CTA composited, not at the end of the tile's
+  // list: with early termination (deep tiles, opaque scenes) almost all of the list lies behind it and
+  // must not even be staged.
+  __shared__ int sFinal;
+  if (threadIdx.x == 0) sFinal = -1;
+  __syncthreads();
+  if (lane == 0) atomicMax(&sFinal, warp_final);
+  __syncthreads();
+  const int list_end = min(range.y, sFinal + 1);
+  const int walk = list_end - range.x;
+  if (walk <= 0) return;
   // v_alpha = T * (rgb . v_out) - ra * acc,  acc = sum_{behind} fac_j (rgb_j . v_out) - T_final (v_out_alpha - bg . v_out)
   float T = T_final;
   float acc = -T_final * (vo_a - bg_dot);
@@ -102,11 +113,11 @@ __global__ void __launch_bounds__(NW * 32) raster_bwd_kernel(
   float own_x = 0.f, own_y = 0.f;
   int own_g = 0;
 
-  for (int b0 = 0; b0 < count; b0 += kB) {
+  for (int b0 = 0; b0 < walk; b0 += kB) {
     __syncthreads();
-    const int bsize = min(kB, count - b0);
+    const int bsize = min(kB, walk - b0);
     if (threadIdx.x < bsize) {
-      const int g = __ldg(ids_sorted + range.y - 1 - b0 - threadIdx.x);   // slot s <-> idx = end-1-b0-s
+      const int g = __ldg(ids_sorted + list_end - 1 - b0 - threadIdx.x);   // slot s <-> idx = list_end-1-b0-s
       const float4* p = vp + (size_t)g * 3;
       sA[threadIdx.x] = __ldg(p); sB[threadIdx.x] = __ldg(p + 1); sC[threadIdx.x] = __ldg(p + 2);
       sG[threadIdx.x] = g;
@@ -114,7 +125,7 @@ __global__ void __launch_bounds__(NW * 32) raster_bwd_kernel(
     __syncthreads();
     for (int c0 = 0; c0 < bsize; c0 += 32) {
       // everything at list positions above the warp's last composited Gaussian is untouched
-      const int hi_idx = range.y - 1 - b0 - c0;       // list index of slot c0
+      const int hi_idx = list_end - 1 - b0 - c0;      // list index of slot c0
       if (hi_idx - 31 > warp_final) continue;
       const int j = c0 + lane;
       bool hit = false;
@@ -123,7 +134,7 @@ __global__ void __launch_bounds__(NW * 32) raster_bwd_kernel(
       while (mask) {
         const int k = c0 + __ffs(mask) - 1;
         mask &= mask - 1;
-        const int idx = range.y - 1 - b0 - k;
+        const int idx = list_end - 1 - b0 - k;
         const float4 A = sA[k], B = sB[k];
         const float dx = A.x - px, dy = A.y - py;
         const float pw = dx * fmaf(B.y, dy, B.x * dx) + B.z * dy * dy;

@@ -6,6 +6,8 @@ import torch
 from splatformer_b200 import gs_utils, render, synth
 name, views, mode = sys.argv[1], int(sys.argv[2]), sys.argv[3]
 dev = torch.device("cuda:0")
+if os.environ.get("SB_FORCE_GLOBAL"):
+    render.DEFAULT_TILE_CAPACITY = 1 << 20
 gs, cams, gt = synth.make_config(name, 0, num_views=views)
 bw = mode == "fwdbwd"
 raw = {k: v.to(dev).requires_grad_(bw) for k, v in gs.items()}

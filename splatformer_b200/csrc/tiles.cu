@@ -8,28 +8,59 @@
 
 namespace sb {
 
+// One lane per (view, Gaussian).  A Gaussian covering a few tiles writes its own keys; one covering many
+// (large screen radii: tens to hundreds of tiles) is handed to the whole warp, lane = tile, so that its
+// keys and ids leave as coalesced 256-byte / 128-byte stores instead of one 8-byte store per lane and
+// iteration, each to a different sector.
+constexpr int kCoopTiles = 8;
+
 __global__ void __launch_bounds__(256) map_isect_kernel(
     int num_views, int n, const float* __restrict__ xys, int xy_stride, const float* __restrict__ depths,
     const int* __restrict__ radii, const int* __restrict__ cum, int tiles_x, int tiles_y, int bw,
     int64_t* __restrict__ keys, int* __restrict__ gids) {
   const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-  if (i >= (size_t)num_views * n) return;
-  const int r = __ldg(radii + i);
-  if (r <= 0) return;
-  const int v = (int)(i / n);
-  const int g = (int)(i - (size_t)v * n);
-  const float2 c = __ldg(reinterpret_cast<const float2*>(xys + i * xy_stride));
-  int min_x, max_x, min_y, max_y;
-  tile_bbox(c.x, c.y, (float)r, tiles_x, tiles_y, bw, min_x, max_x, min_y, max_y);
-  size_t k = i == 0 ? 0 : (size_t)__ldg(cum + i - 1);
-  const int64_t depth_bits = (int64_t)(uint32_t)__float_as_int(__ldg(depths + i));
-  const int64_t tile0 = (int64_t)v * tiles_x * tiles_y;
-  for (int ty = min_y; ty < max_y; ++ty)
-    for (int tx = min_x; tx < max_x; ++tx) {
-      keys[k] = ((tile0 + (int64_t)ty * tiles_x + tx) << 32) | depth_bits;
-      gids[k] = g;
-      ++k;
+  const int lane = threadIdx.x & 31;
+  int min_x = 0, min_y = 0, nx = 0, total = 0, g = 0;
+  size_t k = 0;
+  int64_t depth_bits = 0, tile0 = 0;
+  if (i < (size_t)num_views * n) {
+    const int r = __ldg(radii + i);
+    if (r > 0) {
+      const int v = (int)(i / n);
+      g = (int)(i - (size_t)v * n);
+      const float2 c = __ldg(reinterpret_cast<const float2*>(xys + i * xy_stride));
+      int max_x, max_y;
+      tile_bbox(c.x, c.y, (float)r, tiles_x, tiles_y, bw, min_x, max_x, min_y, max_y);
+      nx = max_x - min_x;
+      total = nx * (max_y - min_y);
+      k = i == 0 ? 0 : (size_t)__ldg(cum + i - 1);
+      depth_bits = (int64_t)(uint32_t)__float_as_int(__ldg(depths + i));
+      tile0 = (int64_t)v * tiles_x * tiles_y;
     }
+  }
+  if (total > 0 && total <= kCoopTiles) {
+    for (int e = 0; e < total; ++e) {
+      const int ky = e / nx, kx = e - ky * nx;
+      keys[k + e] = ((tile0 + (int64_t)(min_y + ky) * tiles_x + (min_x + kx)) << 32) | depth_bits;
+      gids[k + e] = g;
+    }
+  }
+  unsigned big = __ballot_sync(0xffffffffu, total > kCoopTiles);
+  while (big) {
+    const int src = __ffs(big) - 1;
+    big &= big - 1;
+    const int s_total = __shfl_sync(0xffffffffu, total, src), s_nx = __shfl_sync(0xffffffffu, nx, src);
+    const int s_min_x = __shfl_sync(0xffffffffu, min_x, src), s_min_y = __shfl_sync(0xffffffffu, min_y, src);
+    const int s_g = __shfl_sync(0xffffffffu, g, src);
+    const size_t s_k = __shfl_sync(0xffffffffu, (unsigned long long)k, src);
+    const int64_t s_depth = __shfl_sync(0xffffffffu, (long long)depth_bits, src);
+    const int64_t s_tile0 = __shfl_sync(0xffffffffu, (long long)tile0, src);
+    for (int e = lane; e < s_total; e += 32) {
+      const int ky = e / s_nx, kx = e - ky * s_nx;
+      keys[s_k + e] = ((s_tile0 + (int64_t)(s_min_y + ky) * tiles_x + (s_min_x + kx)) << 32) | s_depth;
+      gids[s_k + e] = s_g;
+    }
+  }
 }
 
 __global__ void __launch_bounds__(256) bin_edges_kernel(int num_isect, const int64_t* __restrict__ keys,

@@ -99,9 +99,29 @@ SB_API int sb_map_gaussian_to_intersects(int num_views, int n, const float* xys,
                                   int tiles_y, int block_width, int64_t* isect_ids,
                                   int* gaussian_ids, sb_stream_t stream);
 
+/* Fused path, global-sort branch: emission in DEPTH ORDER.  sb_depth_order_keys writes, per (view,
+ * Gaussian), key = view << 32 | depth bits and value = the flat index; after a stable sort of those
+ * V*N pairs (sb_sort_pairs, end_bit = 32 + bits(V)) the values are the emission `order`.
+ * sb_gather_i32 reorders the tile counts, sb_cumsum_i32 turns them into offsets, and
+ * sb_map_gaussian_to_intersects_ordered emits slot j = Gaussian order[j].  The emitted keys are then
+ * already ascending in depth within every tile, so the big sort only has to run over the TILE bits
+ * [32, end_bit) (sb_sort_pairs_range, stable): 2 radix passes instead of 6.  Per-tile result:
+ * ascending depth bits, ties by ascending Gaussian id -- identical to sorting the full 64-bit key. */
+SB_API int sb_depth_order_keys(int num_views, int n, const float* depths, const int* radii, int64_t* keys,
+                        int* index, sb_stream_t stream);
+SB_API int sb_gather_i32(int count, const int* src, const int* index, int* dst, sb_stream_t stream);
+SB_API int sb_map_gaussian_to_intersects_ordered(int num_views, int n, const float* xys, int xys_stride,
+                                          const float* depths, const int* radii, const int* order,
+                                          const int* cum_tiles_hit_ordered, int tiles_x, int tiles_y,
+                                          int block_width, int64_t* isect_ids, int* gaussian_ids,
+                                          sb_stream_t stream);
+
 /* ---- a7: the 64-bit (tile|depth) key sort (upstream: torch.sort + torch.gather) --------
  * stable LSD radix sort of (key, value) pairs over key bits [0, end_bit). */
 SB_API size_t sb_sort_temp_bytes(int num_intersects);
+SB_API int sb_sort_pairs_range(int count, int begin_bit, int end_bit, const int64_t* keys_in,
+                        const int* vals_in, int64_t* keys_out, int* vals_out, void* temp,
+                        size_t temp_bytes, sb_stream_t stream);
 SB_API int sb_sort_pairs(int num_intersects, int end_bit, const int64_t* keys_in, const int* vals_in,
                   int64_t* keys_out, int* vals_out, void* temp, size_t temp_bytes,
                   sb_stream_t stream);

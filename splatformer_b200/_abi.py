@@ -33,6 +33,10 @@ SIGNATURES = {
     "sb_cumsum_temp_bytes": (S, [I]),
     "sb_cumsum_i32": (I, [I, P, P, P, S, P]),
     "sb_map_gaussian_to_intersects": (I, [I, I, P, I, P, P, P, I, I, I, P, P, P]),
+    "sb_depth_order_keys": (I, [I, I, P, P, P, P, P]),
+    "sb_gather_i32": (I, [I, P, P, P, P]),
+    "sb_map_gaussian_to_intersects_ordered": (I, [I, I, P, I, P, P, P, P, I, I, I, P, P, P]),
+    "sb_sort_pairs_range": (I, [I, I, I, P, P, P, P, P, S, P]),
     "sb_sort_temp_bytes": (S, [I]),
     "sb_sort_pairs": (I, [I, I, P, P, P, P, P, S, P]),
     "sb_tile_bin_edges": (I, [I, P, I, P, P]),

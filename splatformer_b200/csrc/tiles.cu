@@ -17,13 +17,17 @@ constexpr int kCoopTiles = 8;
 __global__ void __launch_bounds__(256) map_isect_kernel(
     int num_views, int n, const float* __restrict__ xys, int xy_stride, const float* __restrict__ depths,
     const int* __restrict__ radii, const int* __restrict__ cum, int tiles_x, int tiles_y, int bw,
-    int64_t* __restrict__ keys, int* __restrict__ gids) {
-  const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    int64_t* __restrict__ keys, int* __restrict__ gids, const int* __restrict__ order) {
+  // slot j of the emission order handles (view, Gaussian) index i = order[j] (identity without `order`);
+  // cum is the prefix sum of the tile counts in emission order
+  const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;
+  const bool in_range = j < (size_t)num_views * n;
+  const size_t i = (order && in_range) ? (size_t)__ldg(order + j) : j;
   const int lane = threadIdx.x & 31;
   int min_x = 0, min_y = 0, nx = 0, total = 0, g = 0;
   size_t k = 0;
   int64_t depth_bits = 0, tile0 = 0;
-  if (i < (size_t)num_views * n) {
+  if (in_range) {
     const int r = __ldg(radii + i);
     if (r > 0) {
       const int v = (int)(i / n);
@@ -33,7 +37,7 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
       tile_bbox(c.x, c.y, (float)r, tiles_x, tiles_y, bw, min_x, max_x, min_y, max_y);
       nx = max_x - min_x;
       total = nx * (max_y - min_y);
-      k = i == 0 ? 0 : (size_t)__ldg(cum + i - 1);
+      k = j == 0 ? 0 : (size_t)__ldg(cum + j - 1);
       depth_bits = (int64_t)(uint32_t)__float_as_int(__ldg(depths + i));
       tile0 = (int64_t)v * tiles_x * tiles_y;
     }
@@ -61,6 +65,26 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
       gids[s_k + e] = s_g;
     }
   }
+}
+
+// Depth pre-order of the fused path's global sort (tiles.cu: sb_depth_order_keys): key = view << 32 |
+// float32 bits of the depth (culled Gaussians: all ones in the low word -- they emit nothing, their place
+// does not matter), value = flat (view, Gaussian) index.
+__global__ void __launch_bounds__(256) depth_keys_kernel(int num_views, int n, const float* __restrict__ depths,
+                                                         const int* __restrict__ radii, int64_t* __restrict__ keys,
+                                                         int* __restrict__ index) {
+  const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= (size_t)num_views * n) return;
+  const int64_t v = (int64_t)(i / n);
+  const uint32_t bits = __ldg(radii + i) > 0 ? (uint32_t)__float_as_int(__ldg(depths + i)) : 0xffffffffu;
+  keys[i] = (v << 32) | (int64_t)bits;
+  index[i] = (int)i;
+}
+
+__global__ void __launch_bounds__(256) gather_i32_kernel(int count, const int* __restrict__ src,
+                                                         const int* __restrict__ index, int* __restrict__ dst) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < count) dst[i] = __ldg(src + __ldg(index + i));
 }
 
 __global__ void __launch_bounds__(256) bin_edges_kernel(int num_isect, const int64_t* __restrict__ keys,
@@ -104,7 +128,39 @@ extern "C" int sb_map_gaussian_to_intersects(int num_views, int n, const float* 
   if (total == 0) return 0;
   sb::map_isect_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit, tiles_x, tiles_y, block_width, isect_ids,
-      gaussian_ids);
+      gaussian_ids, nullptr);
+  SB_RETURN_LAST();
+}
+
+extern "C" int sb_map_gaussian_to_intersects_ordered(int num_views, int n, const float* xys, int xys_stride,
+                                                     const float* depths, const int* radii, const int* order,
+                                                     const int* cum_tiles_hit_ordered, int tiles_x, int tiles_y,
+                                                     int block_width, int64_t* isect_ids, int* gaussian_ids,
+                                                     sb_stream_t stream) {
+  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || xys_stride < 2 || (xys_stride & 1) || !order)
+    return SB_ERR_BAD_ARG;
+  const size_t total = (size_t)num_views * n;
+  if (total == 0) return 0;
+  sb::map_isect_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit_ordered, tiles_x, tiles_y, block_width, isect_ids,
+      gaussian_ids, order);
+  SB_RETURN_LAST();
+}
+
+extern "C" int sb_depth_order_keys(int num_views, int n, const float* depths, const int* radii, int64_t* keys,
+                                   int* index, sb_stream_t stream) {
+  if (n < 0 || num_views < 1) return SB_ERR_BAD_ARG;
+  const size_t total = (size_t)num_views * n;
+  if (total == 0) return 0;
+  sb::depth_keys_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(num_views, n, depths,
+                                                                                          radii, keys, index);
+  SB_RETURN_LAST();
+}
+
+extern "C" int sb_gather_i32(int count, const int* src, const int* index, int* dst, sb_stream_t stream) {
+  if (count < 0) return SB_ERR_BAD_ARG;
+  if (count == 0) return 0;
+  sb::gather_i32_kernel<<<sb::ceil_div(count, 256), 256, 0, (cudaStream_t)stream>>>(count, src, index, dst);
   SB_RETURN_LAST();
 }
 
@@ -123,6 +179,16 @@ extern "C" int sb_sort_pairs(int num_intersects, int end_bit, const int64_t* key
   if (temp_bytes < sb_sort_temp_bytes(num_intersects)) return SB_ERR_TEMP_TOO_SMALL;
   return (int)cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out,
                                               num_intersects, 0, end_bit, (cudaStream_t)stream);
+}
+
+extern "C" int sb_sort_pairs_range(int count, int begin_bit, int end_bit, const int64_t* keys_in,
+                                   const int* vals_in, int64_t* keys_out, int* vals_out, void* temp,
+                                   size_t temp_bytes, sb_stream_t stream) {
+  if (count < 0 || begin_bit < 0 || end_bit <= begin_bit || end_bit > 64) return SB_ERR_BAD_ARG;
+  if (count == 0) return 0;
+  if (temp_bytes < sb_sort_temp_bytes(count)) return SB_ERR_TEMP_TOO_SMALL;
+  return (int)cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, count,
+                                              begin_bit, end_bit, (cudaStream_t)stream);
 }
 
 extern "C" int sb_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted,

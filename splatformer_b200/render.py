@@ -85,6 +85,12 @@ _pinned: Dict[int, Tensor] = {}
 _overflowed: Dict[Tuple[int, int, int], int] = {}
 USE_RECT_LISTS = True               # fused path, block width 16: rect-list rasteriser (csrc/raster_rect.cu)
 DEFAULT_TILE_CAPACITY = 2048        # doubled per overflow of a (views, tiles, Gaussians) shape, up to the library's limit
+# Scenes whose Gaussians cover many tiles each (large screen radii: a room seen from inside, the 4K stress
+# shape) are binned faster by the depth-ordered global sort than by per-tile slot claims -- hundreds of
+# millions of contended atomics and scattered 8-byte stores.  A shape that averaged more tiles per
+# (view, Gaussian) than this goes to the global sort from its next call on.
+GLOBAL_SORT_TILES_PER_GAUSSIAN = 16.0
+_prefer_global: Dict[Tuple[int, int, int], bool] = {}
 
 
 def _pinned_pair(device) -> Tensor:
@@ -98,6 +104,8 @@ def _tile_capacity(lib, v: int, num_tiles: int, n: int) -> int:
     """Segment capacity for the tile sort, or 0 to use the global sort.  A (views, tiles, Gaussians)
     shape whose tiles overflowed the capacity gets twice the capacity next time; past the library's
     limit it goes straight to the global sort."""
+    if _prefer_global.get((v, num_tiles, n)):
+        return 0
     cap = DEFAULT_TILE_CAPACITY << _overflowed.get((v, num_tiles, n), 0)
     if cap > lib.sb_tile_sort_capacity() or v * num_tiles * cap >= 2 ** 31:
         return 0
@@ -247,6 +255,8 @@ class _RenderViews(Function):
             flag_ready.synchronize()
             num_intersects, overflow = int(host_totals[0]), int(host_totals[1])
             done = overflow == 0
+            if num_intersects > GLOBAL_SORT_TILES_PER_GAUSSIAN * v * n:
+                _prefer_global[(v, num_tiles, n)] = True
             if not done:
                 _note_overflow(v, num_tiles, n)
                 rect_ids = rect_counts = None
@@ -254,17 +264,11 @@ class _RenderViews(Function):
             # very deep tiles: global 64-bit (tile | depth) radix sort, as the per-view API does
             if not cap:
                 project(None, None, 0)
-            with _stage("cumsum"):
-                num_intersects, cum = utils.compute_cumulative_intersects(tiles_hit)
-            with _stage("map_isect"):
-                isect_ids, gaussian_ids = _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x,
-                                               tiles_y, block_width)
-            with _stage("sort"):
-                isect_sorted, gids_sorted = utils.sort_isects(isect_ids, gaussian_ids, num_tiles * v)
-            with _stage("bin_edges"):
-                tile_bins = utils.get_tile_bin_edges(num_intersects, isect_sorted, (tiles_x, tiles_y, 1), v)
-            ends = cum.view(v, n)[:, -1]
-            view_has = (torch.diff(ends, prepend=ends.new_zeros(1)) > 0).to(I32)
+            # depth pre-order of the Gaussians, emission in that order, radix sort over the tile bits only
+            with _stage("global_sort"):
+                num_intersects, _, gids_sorted, tile_bins, view_ends = utils.bin_depth_ordered(
+                    v, n, packed, 12, depths.view(-1), radii.view(-1), tiles_hit, (tiles_x, tiles_y, 1), block_width)
+            view_has = (torch.diff(view_ends, prepend=view_ends.new_zeros(1)) > 0).to(I32)
             raster(gids_sorted, tile_bins, view_has)
         _last_num_intersects = num_intersects
         ctx.meta = (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride,

@@ -111,3 +111,59 @@ def bin_and_sort_gaussians(num_points: int, num_intersects: int, xys: Tensor, de
     isect_ids_sorted, gaussian_ids_sorted = sort_isects(isect_ids, gaussian_ids, tiles)
     tile_bins = get_tile_bin_edges(num_intersects, isect_ids_sorted, tile_bounds, num_views)
     return isect_ids, gaussian_ids, isect_ids_sorted, gaussian_ids_sorted, tile_bins
+
+
+def bin_depth_ordered(num_views: int, n: int, xys: Tensor, xys_stride: int, depths: Tensor, radii: Tensor,
+                      num_tiles_hit: Tensor, tile_bounds, block_width: int):
+    """The fused path's global sort (render.py): same per-tile lists as bin_and_sort_gaussians, built as
+    depth pre-order of the V*N Gaussians (a small sort) -> emission in that order -> stable radix sort
+    over the TILE bits only.  The emitted keys are already ascending in depth inside every tile, so the
+    big sort needs 2 radix passes over bits [32, 32 + bits(V*T)) instead of 6 over the whole key.
+    Returns (num_intersects, isect_ids_sorted, gaussian_ids_sorted, tile_bins, last cumulative count per view)."""
+    lib = _abi.load()
+    dev = depths.device
+    total = num_views * n
+    I64, I32, F32 = torch.int64, torch.int32, torch.float32
+    dkeys = torch.empty(total, dtype=I64, device=dev)
+    index = torch.empty(total, dtype=I32, device=dev)
+    _abi.check(lib.sb_depth_order_keys(num_views, n, _abi.ptr(depths, F32, "depths"), _abi.ptr(radii, I32, "radii"),
+                                       _abi.ptr(dkeys, I64, "depth_keys"), _abi.ptr(index, I32, "index"),
+                                       _abi.stream()), "sb_depth_order_keys")
+    dkeys_sorted, order = torch.empty_like(dkeys), torch.empty_like(index)
+    tmp = _scratch(lib.sb_sort_temp_bytes(total), dev)
+    view_bits = max(1, (max(num_views, 1) - 1).bit_length())
+    _abi.check(lib.sb_sort_pairs(total, 32 + view_bits, _abi.ptr(dkeys, I64, "depth_keys"),
+                                 _abi.ptr(index, I32, "index"), _abi.ptr(dkeys_sorted, I64, "depth_keys_sorted"),
+                                 _abi.ptr(order, I32, "order"), _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(),
+                                 _abi.stream()), "sb_sort_pairs")
+    del dkeys, dkeys_sorted, index
+    hit_ordered = torch.empty(total, dtype=I32, device=dev)
+    _abi.check(lib.sb_gather_i32(total, _abi.ptr(num_tiles_hit.view(-1), I32, "num_tiles_hit"),
+                                 _abi.ptr(order, I32, "order"), _abi.ptr(hit_ordered, I32, "hit_ordered"),
+                                 _abi.stream()), "sb_gather_i32")
+    num_intersects, cum = compute_cumulative_intersects(hit_ordered)
+    tiles_x, tiles_y = int(tile_bounds[0]), int(tile_bounds[1])
+    isect_ids = torch.empty(num_intersects, dtype=I64, device=dev)
+    gaussian_ids = torch.empty(num_intersects, dtype=I32, device=dev)
+    if num_intersects > 0:
+        _abi.check(lib.sb_map_gaussian_to_intersects_ordered(
+            num_views, n, _abi.ptr(xys, F32, "xys"), xys_stride, _abi.ptr(depths, F32, "depths"),
+            _abi.ptr(radii, I32, "radii"), _abi.ptr(order, I32, "order"), _abi.ptr(cum, I32, "cum_tiles_hit"),
+            tiles_x, tiles_y, block_width, _abi.ptr(isect_ids, I64, "isect_ids"),
+            _abi.ptr(gaussian_ids, I32, "gaussian_ids"), _abi.stream()), "sb_map_gaussian_to_intersects_ordered")
+    tiles_total = tiles_x * tiles_y * num_views
+    keys_out, vals_out = torch.empty_like(isect_ids), torch.empty_like(gaussian_ids)
+    if num_intersects > 0:
+        end_bit = 32 + max(1, (max(tiles_total, 1) - 1).bit_length())
+        tmp = _scratch(lib.sb_sort_temp_bytes(num_intersects), dev)
+        _abi.check(lib.sb_sort_pairs_range(num_intersects, 32, end_bit, _abi.ptr(isect_ids, I64, "isect_ids"),
+                                           _abi.ptr(gaussian_ids, I32, "gaussian_ids"),
+                                           _abi.ptr(keys_out, I64, "isect_ids_sorted"),
+                                           _abi.ptr(vals_out, I32, "gaussian_ids_sorted"),
+                                           _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()),
+                   "sb_sort_pairs_range")
+    del isect_ids, gaussian_ids
+    tile_bins = get_tile_bin_edges(num_intersects, keys_out, tile_bounds, num_views)
+    # emission is view-major (the view is the top of the pre-order key): offsets at the view boundaries
+    view_ends = cum.view(num_views, n)[:, -1] if total > 0 else cum
+    return num_intersects, keys_out, vals_out, tile_bins, view_ends

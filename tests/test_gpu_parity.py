@@ -274,3 +274,33 @@ def test_compute_cov2d_bounds(cuda, sb_lib):
     # the kernel rounds once per operation like the oracle's float32 chain: identical bits
     assert torch.equal(conic.cpu(), conic_ref)
     assert torch.equal(radius.cpu(), radius_ref)
+
+
+@pytest.mark.parametrize("n,size,views,mult", [(3000, (200, 120), 3, 0.3), (800, (64, 48), 2, 2.5)])
+def test_depth_ordered_binning_equals_full_key_sort(cuda, sb_lib, n, size, views, mult):
+    """The fused path's global sort (depth pre-order + emission + radix sort over the tile bits only) gives
+    the same sorted keys, ids and bins as sorting the whole 64-bit key (= the oracle's order: ascending
+    depth bits per tile, ties by ascending id)."""
+    from splatformer_b200 import utils as U
+    gs, cams = _scene(n, 0, size, mult, views=views)
+    gs["means"][: n // 40] = gs["means"][0]                     # exact depth ties
+    k = H.cam_scalars(cams)
+    a = H.activated(gs, cuda)
+    tb = ((k["W"] + 15) // 16, (k["H"] + 15) // 16, 1)
+    outs = []
+    for v in range(views):
+        vm = R.viewmat_from_c2w(cams["camera_to_worlds"][v])[:3].contiguous().to(cuda)
+        outs.append(gsplat.project_gaussians(a["means"], a["scales"], 1, a["quats"], vm, k["fx"], k["fy"], k["cx"],
+                                             k["cy"], k["H"], k["W"], 16))
+    xys = torch.stack([o[0] for o in outs]).contiguous()
+    depths = torch.stack([o[1] for o in outs]).contiguous()
+    radii = torch.stack([o[2] for o in outs]).contiguous()
+    tiles = torch.stack([o[5] for o in outs]).contiguous()
+    ni, cum = U.compute_cumulative_intersects(tiles)
+    _, _, keys_ref, ids_ref, bins_ref = U.bin_and_sort_gaussians(n, ni, xys.view(-1, 2), depths.view(-1),
+                                                                 radii.view(-1), cum, tb, 16, num_views=views)
+    ni2, keys, ids, bins, view_ends = U.bin_depth_ordered(views, n, xys.view(-1, 2), 2, depths.view(-1),
+                                                          radii.view(-1), tiles, tb, 16)
+    assert ni2 == ni and ni > 2 * n
+    assert torch.equal(keys, keys_ref) and torch.equal(ids, ids_ref) and torch.equal(bins, bins_ref)
+    assert torch.equal(view_ends.cpu(), cum.view(views, n)[:, -1].cpu())

@@ -116,6 +116,19 @@ SB_API int sb_map_gaussian_to_intersects_ordered(int num_views, int n, const flo
                                           int block_width, int64_t* isect_ids, int* gaussian_ids,
                                           sb_stream_t stream);
 
+/* Compact variant of the same branch (what render.py uses): with depth-ordered emission the key only has
+ * to carry the tile, so it is a uint32 (view*T + tile): 8 bytes per pair through the sort instead of 12. */
+SB_API int sb_map_gaussian_to_tiles_ordered(int num_views, int n, const float* xys, int xys_stride,
+                                     const float* depths, const int* radii, const int* order,
+                                     const int* cum_tiles_hit_ordered, int tiles_x, int tiles_y,
+                                     int block_width, uint32_t* tile_ids, int* gaussian_ids,
+                                     sb_stream_t stream);
+SB_API size_t sb_sort32_temp_bytes(int count);
+SB_API int sb_sort_pairs32(int count, int end_bit, const uint32_t* keys_in, const int* vals_in,
+                    uint32_t* keys_out, int* vals_out, void* temp, size_t temp_bytes, sb_stream_t stream);
+SB_API int sb_tile_bin_edges32(int count, const uint32_t* tile_ids_sorted, int num_tiles_total, int* tile_bins,
+                        sb_stream_t stream);
+
 /* ---- a7: the 64-bit (tile|depth) key sort (upstream: torch.sort + torch.gather) --------
  * stable LSD radix sort of (key, value) pairs over key bits [0, end_bit). */
 SB_API size_t sb_sort_temp_bytes(int num_intersects);

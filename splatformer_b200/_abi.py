@@ -37,6 +37,10 @@ SIGNATURES = {
     "sb_gather_i32": (I, [I, P, P, P, P]),
     "sb_map_gaussian_to_intersects_ordered": (I, [I, I, P, I, P, P, P, P, I, I, I, P, P, P]),
     "sb_sort_pairs_range": (I, [I, I, I, P, P, P, P, P, S, P]),
+    "sb_map_gaussian_to_tiles_ordered": (I, [I, I, P, I, P, P, P, P, I, I, I, P, P, P]),
+    "sb_sort32_temp_bytes": (S, [I]),
+    "sb_sort_pairs32": (I, [I, I, P, P, P, P, P, S, P]),
+    "sb_tile_bin_edges32": (I, [I, P, I, P, P]),
     "sb_sort_temp_bytes": (S, [I]),
     "sb_sort_pairs": (I, [I, I, P, P, P, P, P, S, P]),
     "sb_tile_bin_edges": (I, [I, P, I, P, P]),

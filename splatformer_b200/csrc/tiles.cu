@@ -14,10 +14,14 @@ namespace sb {
 // iteration, each to a different sector.
 constexpr int kCoopTiles = 8;
 
+// COMPACT: the key is the 32-bit tile index alone (depth-ordered emission: the depth is already encoded in
+// the position), stored through the same pointer reinterpreted as uint32.
+template <bool COMPACT>
 __global__ void __launch_bounds__(256) map_isect_kernel(
     int num_views, int n, const float* __restrict__ xys, int xy_stride, const float* __restrict__ depths,
     const int* __restrict__ radii, const int* __restrict__ cum, int tiles_x, int tiles_y, int bw,
     int64_t* __restrict__ keys, int* __restrict__ gids, const int* __restrict__ order) {
+  uint32_t* keys32 = reinterpret_cast<uint32_t*>(keys);
   // slot j of the emission order handles (view, Gaussian) index i = order[j] (identity without `order`);
   // cum is the prefix sum of the tile counts in emission order
   const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;
@@ -45,7 +49,8 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
   if (total > 0 && total <= kCoopTiles) {
     for (int e = 0; e < total; ++e) {
       const int ky = e / nx, kx = e - ky * nx;
-      keys[k + e] = ((tile0 + (int64_t)(min_y + ky) * tiles_x + (min_x + kx)) << 32) | depth_bits;
+      const int64_t t = tile0 + (int64_t)(min_y + ky) * tiles_x + (min_x + kx);
+      if (COMPACT) keys32[k + e] = (uint32_t)t; else keys[k + e] = (t << 32) | depth_bits;
       gids[k + e] = g;
     }
   }
@@ -61,7 +66,8 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
     const int64_t s_tile0 = __shfl_sync(0xffffffffu, (long long)tile0, src);
     for (int e = lane; e < s_total; e += 32) {
       const int ky = e / s_nx, kx = e - ky * s_nx;
-      keys[s_k + e] = ((s_tile0 + (int64_t)(s_min_y + ky) * tiles_x + (s_min_x + kx)) << 32) | s_depth;
+      const int64_t t = s_tile0 + (int64_t)(s_min_y + ky) * tiles_x + (s_min_x + kx);
+      if (COMPACT) keys32[s_k + e] = (uint32_t)t; else keys[s_k + e] = (t << 32) | s_depth;
       gids[s_k + e] = s_g;
     }
   }
@@ -100,6 +106,19 @@ __global__ void __launch_bounds__(256) bin_edges_kernel(int num_isect, const int
   if (idx == num_isect - 1) bins[cur].y = num_isect;
 }
 
+__global__ void __launch_bounds__(256) bin_edges32_kernel(int count, const uint32_t* __restrict__ tiles,
+                                                          int2* __restrict__ bins) {
+  const int idx = blockIdx.x * 256 + threadIdx.x;
+  if (idx >= count) return;
+  const int cur = (int)__ldg(tiles + idx);
+  if (idx == 0) bins[cur].x = 0;
+  else {
+    const int prev = (int)__ldg(tiles + idx - 1);
+    if (prev != cur) { bins[prev].y = idx; bins[cur].x = idx; }
+  }
+  if (idx == count - 1) bins[cur].y = count;
+}
+
 }  // namespace sb
 
 extern "C" size_t sb_cumsum_temp_bytes(int count) {
@@ -126,7 +145,7 @@ extern "C" int sb_map_gaussian_to_intersects(int num_views, int n, const float* 
     return SB_ERR_BAD_ARG;
   const size_t total = (size_t)num_views * n;
   if (total == 0) return 0;
-  sb::map_isect_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+  sb::map_isect_kernel<false><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit, tiles_x, tiles_y, block_width, isect_ids,
       gaussian_ids, nullptr);
   SB_RETURN_LAST();
@@ -141,9 +160,50 @@ extern "C" int sb_map_gaussian_to_intersects_ordered(int num_views, int n, const
     return SB_ERR_BAD_ARG;
   const size_t total = (size_t)num_views * n;
   if (total == 0) return 0;
-  sb::map_isect_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+  sb::map_isect_kernel<false><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit_ordered, tiles_x, tiles_y, block_width, isect_ids,
       gaussian_ids, order);
+  SB_RETURN_LAST();
+}
+
+extern "C" int sb_map_gaussian_to_tiles_ordered(int num_views, int n, const float* xys, int xys_stride,
+                                                const float* depths, const int* radii, const int* order,
+                                                const int* cum_tiles_hit_ordered, int tiles_x, int tiles_y,
+                                                int block_width, uint32_t* tile_ids, int* gaussian_ids,
+                                                sb_stream_t stream) {
+  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || xys_stride < 2 || (xys_stride & 1) || !order)
+    return SB_ERR_BAD_ARG;
+  const size_t total = (size_t)num_views * n;
+  if (total == 0) return 0;
+  sb::map_isect_kernel<true><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit_ordered, tiles_x, tiles_y, block_width,
+      reinterpret_cast<int64_t*>(tile_ids), gaussian_ids, order);
+  SB_RETURN_LAST();
+}
+
+extern "C" size_t sb_sort32_temp_bytes(int count) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const int*)nullptr,
+                                  (int*)nullptr, count, 0, 32);
+  return bytes;
+}
+
+extern "C" int sb_sort_pairs32(int count, int end_bit, const uint32_t* keys_in, const int* vals_in,
+                               uint32_t* keys_out, int* vals_out, void* temp, size_t temp_bytes,
+                               sb_stream_t stream) {
+  if (count < 0 || end_bit < 1 || end_bit > 32) return SB_ERR_BAD_ARG;
+  if (count == 0) return 0;
+  if (temp_bytes < sb_sort32_temp_bytes(count)) return SB_ERR_TEMP_TOO_SMALL;
+  return (int)cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, count, 0,
+                                              end_bit, (cudaStream_t)stream);
+}
+
+extern "C" int sb_tile_bin_edges32(int count, const uint32_t* tile_ids_sorted, int num_tiles_total, int* tile_bins,
+                                   sb_stream_t stream) {
+  if (count < 0 || num_tiles_total < 0) return SB_ERR_BAD_ARG;
+  if (count == 0) return 0;
+  sb::bin_edges32_kernel<<<sb::ceil_div(count, 256), 256, 0, (cudaStream_t)stream>>>(
+      count, tile_ids_sorted, reinterpret_cast<int2*>(tile_bins));
   SB_RETURN_LAST();
 }
 

@@ -261,13 +261,14 @@ class _RenderViews(Function):
                 _note_overflow(v, num_tiles, n)
                 rect_ids = rect_counts = None
         if not done:
-            # very deep tiles: global 64-bit (tile | depth) radix sort, as the per-view API does
+            # very deep tiles / many tiles per Gaussian: global sort over all (tile, Gaussian) pairs
             if not cap:
                 project(None, None, 0)
             # depth pre-order of the Gaussians, emission in that order, radix sort over the tile bits only
             with _stage("global_sort"):
                 num_intersects, _, gids_sorted, tile_bins, view_ends = utils.bin_depth_ordered(
-                    v, n, packed, 12, depths.view(-1), radii.view(-1), tiles_hit, (tiles_x, tiles_y, 1), block_width)
+                    v, n, packed, 12, depths.view(-1), radii.view(-1), tiles_hit, (tiles_x, tiles_y, 1), block_width,
+                    compact=True)
             view_has = (torch.diff(view_ends, prepend=view_ends.new_zeros(1)) > 0).to(I32)
             raster(gids_sorted, tile_bins, view_has)
         _last_num_intersects = num_intersects
@@ -350,13 +351,6 @@ class _RenderViews(Function):
                 _abi.ptr(v_opac, F32, "v_opacities"), _abi.ptr(v_color, F32, "v_color_src"),
                 _abi.ptr(v_rest, F32, "v_color_rest"), _abi.stream()), "sb_views_project_bwd")
         return (v_means, v_scales, v_quats, v_opac, v_color, v_rest) + (None,) * (nin - 6)
-
-
-def _map(lib, v, n, packed, depths, radii, cum, num_intersects, tiles_x, tiles_y, block_width):
-    """Key emission for the batched path reads the pixel centres straight out of the packed record
-    (stride 12 floats)."""
-    return utils.map_gaussian_to_intersects(n, num_intersects, packed, depths.view(-1), radii.view(-1), cum,
-                                            (tiles_x, tiles_y, 1), block_width, num_views=v, xys_stride=12)
 
 
 def render_views(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor, color_src: Tensor,

@@ -114,11 +114,13 @@ def bin_and_sort_gaussians(num_points: int, num_intersects: int, xys: Tensor, de
 
 
 def bin_depth_ordered(num_views: int, n: int, xys: Tensor, xys_stride: int, depths: Tensor, radii: Tensor,
-                      num_tiles_hit: Tensor, tile_bounds, block_width: int):
+                      num_tiles_hit: Tensor, tile_bounds, block_width: int, compact: bool = False):
     """The fused path's global sort (render.py): same per-tile lists as bin_and_sort_gaussians, built as
     depth pre-order of the V*N Gaussians (a small sort) -> emission in that order -> stable radix sort
     over the TILE bits only.  The emitted keys are already ascending in depth inside every tile, so the
     big sort needs 2 radix passes over bits [32, 32 + bits(V*T)) instead of 6 over the whole key.
+    compact=True carries only the uint32 tile index through the big sort (8 bytes per pair instead of 12)
+    and returns the sorted tile indices in place of the 64-bit keys.
     Returns (num_intersects, isect_ids_sorted, gaussian_ids_sorted, tile_bins, last cumulative count per view)."""
     lib = _abi.load()
     dev = depths.device
@@ -143,27 +145,44 @@ def bin_depth_ordered(num_views: int, n: int, xys: Tensor, xys_stride: int, dept
                                  _abi.stream()), "sb_gather_i32")
     num_intersects, cum = compute_cumulative_intersects(hit_ordered)
     tiles_x, tiles_y = int(tile_bounds[0]), int(tile_bounds[1])
-    isect_ids = torch.empty(num_intersects, dtype=I64, device=dev)
-    gaussian_ids = torch.empty(num_intersects, dtype=I32, device=dev)
-    if num_intersects > 0:
-        _abi.check(lib.sb_map_gaussian_to_intersects_ordered(
-            num_views, n, _abi.ptr(xys, F32, "xys"), xys_stride, _abi.ptr(depths, F32, "depths"),
-            _abi.ptr(radii, I32, "radii"), _abi.ptr(order, I32, "order"), _abi.ptr(cum, I32, "cum_tiles_hit"),
-            tiles_x, tiles_y, block_width, _abi.ptr(isect_ids, I64, "isect_ids"),
-            _abi.ptr(gaussian_ids, I32, "gaussian_ids"), _abi.stream()), "sb_map_gaussian_to_intersects_ordered")
     tiles_total = tiles_x * tiles_y * num_views
+    tile_bits = max(1, (max(tiles_total, 1) - 1).bit_length())
+    kdt = torch.int32 if compact else I64              # int32 storage for the uint32 tile indices
+    isect_ids = torch.empty(num_intersects, dtype=kdt, device=dev)
+    gaussian_ids = torch.empty(num_intersects, dtype=I32, device=dev)
     keys_out, vals_out = torch.empty_like(isect_ids), torch.empty_like(gaussian_ids)
     if num_intersects > 0:
-        end_bit = 32 + max(1, (max(tiles_total, 1) - 1).bit_length())
-        tmp = _scratch(lib.sb_sort_temp_bytes(num_intersects), dev)
-        _abi.check(lib.sb_sort_pairs_range(num_intersects, 32, end_bit, _abi.ptr(isect_ids, I64, "isect_ids"),
+        emit = lib.sb_map_gaussian_to_tiles_ordered if compact else lib.sb_map_gaussian_to_intersects_ordered
+        _abi.check(emit(
+            num_views, n, _abi.ptr(xys, F32, "xys"), xys_stride, _abi.ptr(depths, F32, "depths"),
+            _abi.ptr(radii, I32, "radii"), _abi.ptr(order, I32, "order"), _abi.ptr(cum, I32, "cum_tiles_hit"),
+            tiles_x, tiles_y, block_width, _abi.ptr(isect_ids, kdt, "isect_ids"),
+            _abi.ptr(gaussian_ids, I32, "gaussian_ids"), _abi.stream()), "ordered key emission")
+        if compact:
+            tmp = _scratch(lib.sb_sort32_temp_bytes(num_intersects), dev)
+            _abi.check(lib.sb_sort_pairs32(num_intersects, tile_bits, _abi.ptr(isect_ids, kdt, "tile_ids"),
                                            _abi.ptr(gaussian_ids, I32, "gaussian_ids"),
-                                           _abi.ptr(keys_out, I64, "isect_ids_sorted"),
+                                           _abi.ptr(keys_out, kdt, "tile_ids_sorted"),
                                            _abi.ptr(vals_out, I32, "gaussian_ids_sorted"),
                                            _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()),
-                   "sb_sort_pairs_range")
+                       "sb_sort_pairs32")
+        else:
+            tmp = _scratch(lib.sb_sort_temp_bytes(num_intersects), dev)
+            _abi.check(lib.sb_sort_pairs_range(num_intersects, 32, 32 + tile_bits,
+                                               _abi.ptr(isect_ids, I64, "isect_ids"),
+                                               _abi.ptr(gaussian_ids, I32, "gaussian_ids"),
+                                               _abi.ptr(keys_out, I64, "isect_ids_sorted"),
+                                               _abi.ptr(vals_out, I32, "gaussian_ids_sorted"),
+                                               _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()),
+                       "sb_sort_pairs_range")
     del isect_ids, gaussian_ids
-    tile_bins = get_tile_bin_edges(num_intersects, keys_out, tile_bounds, num_views)
+    if compact:
+        tile_bins = torch.zeros(tiles_total, 2, dtype=I32, device=dev)
+        _abi.check(lib.sb_tile_bin_edges32(num_intersects, _abi.ptr(keys_out, kdt, "tile_ids_sorted"), tiles_total,
+                                           _abi.ptr(tile_bins, I32, "tile_bins"), _abi.stream()),
+                   "sb_tile_bin_edges32")
+    else:
+        tile_bins = get_tile_bin_edges(num_intersects, keys_out, tile_bounds, num_views)
     # emission is view-major (the view is the top of the pre-order key): offsets at the view boundaries
     view_ends = cum.view(num_views, n)[:, -1] if total > 0 else cum
     return num_intersects, keys_out, vals_out, tile_bins, view_ends

@@ -304,3 +304,8 @@ def test_depth_ordered_binning_equals_full_key_sort(cuda, sb_lib, n, size, views
     assert ni2 == ni and ni > 2 * n
     assert torch.equal(keys, keys_ref) and torch.equal(ids, ids_ref) and torch.equal(bins, bins_ref)
     assert torch.equal(view_ends.cpu(), cum.view(views, n)[:, -1].cpu())
+    # compact variant (uint32 tile index as the key): same ids and bins, keys = the tile part
+    ni3, tiles_sorted, ids3, bins3, _ = U.bin_depth_ordered(views, n, xys.view(-1, 2), 2, depths.view(-1),
+                                                            radii.view(-1), tiles, tb, 16, compact=True)
+    assert ni3 == ni and torch.equal(ids3, ids_ref) and torch.equal(bins3, bins_ref)
+    assert torch.equal(tiles_sorted.long(), keys_ref >> 32)

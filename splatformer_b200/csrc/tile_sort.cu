@@ -237,7 +237,7 @@ extern "C" int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacit
   if (num_views < 1 || tiles_per_view < 1 || tile_capacity < 64 || tile_capacity > sb::kMaxSegment ||
       (tile_capacity & (tile_capacity - 1)) ||
       (long long)num_views * tiles_per_view * tile_capacity > 2147483647LL ||
-      (rect_ids && (!packed || !rect_counts || tiles_x < 1 || tiles_per_view % tiles_x)))
+      (rect_ids && ((!packed && n > 0) || !rect_counts || tiles_x < 1 || tiles_per_view % tiles_x)))
     return SB_ERR_BAD_ARG;
   const size_t smem = (size_t)tile_capacity * 12;
   if (smem > 40 * 1024)      // the kernel also has a little static shared memory

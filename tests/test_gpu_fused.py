@@ -236,3 +236,19 @@ def test_per_view_wrapper_matches_fused_path(cuda, sb_lib):
     sum((r - g).abs().mean() for r, g in zip(rgbs_b, gt)).backward()
     for name in gs:
         H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name)
+
+
+def test_fused_scene_without_gaussians(cuda, sb_lib):
+    """N = 0 (a scene whose Gaussians were all filtered out): background image, alpha 1 (the upstream
+    empty-frame quirk), empty gradients, no error."""
+    gs = synth.shell_scene(4, 1, seed=1)
+    raw = {k_: v[:0].to(cuda).requires_grad_() for k_, v in gs.items()}
+    cams = {k_: v.to(cuda) for k_, v in synth.orbit_cameras(2, 40, 24, background=(0.2, 0.4, 0.6)).items()}
+    gt = torch.rand(2, 24, 40, 3, device=cuda)
+    l1, mse, img = gs_utils.render_l1_loss(raw, cams, gt, return_images=True)
+    assert torch.allclose(img, cams["background_color"].expand(2, 24, 40, 3))
+    assert torch.allclose(l1, (img - gt).abs().mean(dim=(1, 2, 3)), rtol=1e-5)
+    l1.sum().backward()
+    assert raw["means"].grad is None or raw["means"].grad.shape == (0, 3)
+    rgbs, alphas = gs_utils.rasterize_gaussians_to_multiimgs({k_: v.detach() for k_, v in raw.items()}, cams)
+    assert bool((alphas[0] == 1).all()) and rgbs[1].shape == (24, 40, 3)

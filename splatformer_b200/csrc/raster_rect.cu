@@ -284,24 +284,30 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rec
     rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
   }
   // one list entry, back to front: transmittance / accumulator update and parking of (w, fac)
+  const unsigned wbase = (unsigned)__cvta_generic_to_shared(&sW[warp][lane]);
+  unsigned wcur = wbase;
   auto entry = [&](int idx, float pw, float e, float cr, float cg, float cb, float gx, float gy, int slot) {
     const float alpha_raw = ex2_approx(e);
     const float alpha = fminf(kAlphaMax, alpha_raw);
     const bool valid = (idx <= last) && (pw <= 0.f) && (alpha >= kAlphaMin);
     if (!__any_sync(0xffffffffu, valid)) return;
-    const float ra = rcp_approx(1.0f - alpha);
-    T = valid ? T * ra : T;
-    const float fac = valid ? alpha * T : 0.f;
+    // a lane that skips the entry runs the same arithmetic with alpha = 0 (rcp(1) = 1: T, acc unchanged)
+    const float a = valid ? alpha : 0.f;
+    const float ra = rcp_approx(1.0f - a);
+    T *= ra;
+    const float fac = a * T;
     const float cdot = cr * vo_r + cg * vo_g + cb * vo_b;
     const float v_alpha = T * cdot - ra * acc;
     acc = fmaf(fac, cdot, acc);
-    // d alpha / d sigma = -alpha_raw where the 0.999 clamp is inactive, 0 where it is active
-    const float w = (valid && alpha_raw <= kAlphaMax) ? -alpha_raw * v_alpha : 0.f;
-    sW[warp][nslot * kSlotStride + lane] = make_float2(w, fac);
+    const float aw = (valid && alpha_raw <= kAlphaMax) ? alpha_raw : 0.f;
+    const float w = -aw * v_alpha;
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(wcur), "f"(w), "f"(fac) : "memory");
+    wcur += kSlotStride * (unsigned)sizeof(float2);
     if ((lane & 15) == nslot) { own_x = gx; own_y = gy; own_g = sG[slot]; }
     if (++nslot == kSlots) {
       flush_slots<true>(sW[warp], sVo[warp], nullptr, kSlots, lane, own_x, own_y, own_g, rg.ox, rg.oy, vgrad);
       nslot = 0;
+      wcur = wbase;
     }
   };
   for (; c >= 0; --c) {

@@ -56,8 +56,13 @@ constexpr int kViewsBlock = 128;
 constexpr int kViewLanes = 4;                          // threads that share one Gaussian, each taking V/4 views
 constexpr int kViewsRows = kViewsBlock / kViewLanes;   // Gaussians per block
 
+#ifdef SB_PROJ_FWD_MINB
+#define SB_PROJ_FWD_BOUNDS __launch_bounds__(kViewsBlock, SB_PROJ_FWD_MINB)
+#else
+#define SB_PROJ_FWD_BOUNDS __launch_bounds__(kViewsBlock)
+#endif
 template <int DEG>
-__global__ void __launch_bounds__(kViewsBlock) views_project_fwd_kernel(
+__global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
     int num_views, int n, const float* __restrict__ means, const float* __restrict__ scales, float glob,
     const float* __restrict__ quats, const float* __restrict__ opacities,
     const float* __restrict__ color_src, const float* __restrict__ color_rest, int k3_store, int flags,

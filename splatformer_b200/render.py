@@ -12,6 +12,7 @@ same device functions run underneath.
 from __future__ import annotations
 
 import contextlib
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -72,8 +73,15 @@ def profile_stages():
         _timer = prev
 
 
+_NVTX = bool(os.environ.get("SB_NVTX"))      # SB_NVTX=1: an NVTX range per stage (nsys / ncu --nvtx timelines)
+
+
 def _stage(name: str):
-    return _timer.stage(name) if _timer is not None else contextlib.nullcontext()
+    if _timer is not None:
+        return _timer.stage(name)
+    if _NVTX:
+        return torch.cuda.nvtx.range("sb." + name)
+    return contextlib.nullcontext()
 
 
 def _c(t: Tensor) -> Tensor:

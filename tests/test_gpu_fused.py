@@ -252,3 +252,20 @@ def test_fused_scene_without_gaussians(cuda, sb_lib):
     assert raw["means"].grad is None or raw["means"].grad.shape == (0, 3)
     rgbs, alphas = gs_utils.rasterize_gaussians_to_multiimgs({k_: v.detach() for k_, v in raw.items()}, cams)
     assert bool((alphas[0] == 1).all()) and rgbs[1].shape == (24, 40, 3)
+
+
+def test_fused_loss_under_grad_scaler_magnitudes(cuda, sb_lib):
+    """AMP's GradScaler multiplies the upstream gradient by 2^16 (train.py:215,289): the kernels must not
+    assume |v_out| <= 1 -- gradients scale exactly linearly, nothing overflows."""
+    gs = synth.shell_scene(1500, 2, seed=6, scale_mult=0.3)
+    cams = {k_: v.to(cuda) for k_, v in synth.orbit_cameras(2, 96, 64).items()}
+    gt = synth.target_images(2, 64, 96, seed=3).to(cuda)
+    raw_a = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    raw_b = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    l1_a, _ = gs_utils.render_l1_loss(raw_a, cams, gt)
+    l1_b, _ = gs_utils.render_l1_loss(raw_b, cams, gt)
+    l1_a.mean().backward()
+    (l1_b.mean() * 65536.0).backward()
+    for name in gs:
+        assert torch.isfinite(raw_b[name].grad).all(), name
+        assert H.rel_l2(raw_b[name].grad / 65536.0, raw_a[name].grad) <= 1e-5, name

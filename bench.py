@@ -301,15 +301,23 @@ def main() -> None:
         sync_grads(raw)
         return loss
 
+    # e2e: every step's scene comes from pinned host memory.  splatformer_b200.loader.ScenePrefetcher uploads
+    # scene i+1 on a copy stream while scene i renders (every scene is still copied on every step); the
+    # upload is submitted after the step's kernels have been enqueued, so its host-side cost hides too.
+    from splatformer_b200 import loader as sbloader
+    feeder = sbloader.ScenePrefetcher(dev)
+    e2e_feed = {"ticket": None, "steps": 0}
+
     def step_e2e(i):
-        hgs, hcams, hgt = host[i % NSCENE]
-        raw = {k: v.to(dev, non_blocking=True).requires_grad_() for k, v in hgs.items()}
-        cams = {k: v.to(dev, non_blocking=True) for k, v in hcams.items()}
-        # the pinned host targets go in as they are: render_l1_loss uploads them on a side stream
-        # underneath the projection / sort stages (they are first needed by the raster kernel)
-        loss = render_loss(raw, cams, hgt)
+        if i == 0:      # the loop's first upload is issued here, inside the timed region, and not overlapped
+            e2e_feed["ticket"] = feeder.submit(host[0])
+        gs_d, cams, gt_d = feeder.get(e2e_feed["ticket"])
+        raw = {k: v.requires_grad_() for k, v in gs_d.items()}
+        loss = render_loss(raw, cams, gt_d)
         loss.backward()
         sync_grads(raw)
+        if i + 1 < e2e_feed["steps"]:
+            e2e_feed["ticket"] = feeder.submit(host[(i + 1) % NSCENE])
         return float(loss.item())          # device->host read of the step's result
 
     def barrier():
@@ -347,8 +355,10 @@ def main() -> None:
 
     e2e = None
     if not args.no_e2e:
+        e2e_feed["steps"] = 3
         for i in range(3):
             step_e2e(i)
+        e2e_feed["steps"] = args.steps
         e2e_ms, _, _, _ = timed(step_e2e, args.steps)
     # ---- the unmodified wrapper path: the reference's per-view Python loop on the
     # gsplat-compatible API -- what SplatFormer runs when only `import gsplat` is redirected here
@@ -429,7 +439,8 @@ def main() -> None:
             e2e_step = e2e_ms / args.steps
             line["e2e"] = {"value": pix_step / (e2e_step * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_step,
                            "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4,
-                           "api": "splatformer_b200.gs_utils.render_l1_loss(gs_params, cameras, images) + backward"}
+                           "api": "splatformer_b200.loader.ScenePrefetcher(host scenes) -> gs_utils.render_l1_loss(gs_params, "
+                                  "cameras, images) + backward + loss.item()"}
         if wrapper_ms is not None:
             w_step = wrapper_ms / args.wrapper_steps
             line["wrapper_path"] = {"value": pix_step / (w_step * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": w_step,

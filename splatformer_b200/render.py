@@ -144,6 +144,7 @@ class _RenderViews(Function):
     def forward(ctx, means, scales, quats, opacities, color_src, color_rest, viewmats, campos, intrins, gt,
                 sh_degree, flags, img_height, img_width, block_width, background, clip_thresh, clamp_rgb):
         lib = _abi.load()
+        st = _abi.stream()                      # one current-stream lookup per pass (it costs ~20 us)
         dev = means.device
         n = means.shape[0]
         v = viewmats.shape[0]
@@ -196,7 +197,7 @@ class _RenderViews(Function):
                     clip_thresh, _abi.ptr(packed, F32, "packed"), _abi.ptr(depths, F32, "depths"),
                     _abi.ptr(radii, I32, "radii"), _abi.ptr(tiles_hit, I32, "num_tiles_hit"),
                     _abi.ptr(tile_counts, I32, "tile_counts"), _abi.ptr(tile_keys, torch.int64, "tile_keys"), cap,
-                    _abi.stream()), "sb_views_project_fwd")
+                    st), "sb_views_project_fwd")
 
         def raster_rect(rect_ids, rect_counts, cap, view_has):
             if gt_ready is not None:
@@ -209,7 +210,7 @@ class _RenderViews(Function):
                     _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
                     _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
                     1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,
-                    _abi.ptr(loss_partial, F32, "loss_partial"), _abi.stream()), "sb_rasterize_rect_fwd")
+                    _abi.ptr(loss_partial, F32, "loss_partial"), st), "sb_rasterize_rect_fwd")
 
         def raster(gids_sorted, tile_bins, view_has):
             if gt_ready is not None:
@@ -222,7 +223,7 @@ class _RenderViews(Function):
                     _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
                     _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
                     1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,
-                    _abi.ptr(loss_partial, F32, "loss_partial"), _abi.stream()), "sb_rasterize_fwd")
+                    _abi.ptr(loss_partial, F32, "loss_partial"), st), "sb_rasterize_fwd")
 
         global _last_num_intersects
         cap = _tile_capacity(lib, v, num_tiles, n)
@@ -251,7 +252,7 @@ class _RenderViews(Function):
                     _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(view_has, I32, "view_has_isects"),
                     _abi.ptr(totals, I32, "totals"), n, tiles_x, _abi.ptr(packed, F32, "packed"),
                     _abi.ptr(rect_ids, I32, "rect_ids"), _abi.ptr(rect_counts, I32, "rect_counts"),
-                    _abi.stream()), "sb_sort_tiles")
+                    st), "sb_sort_tiles")
             host_totals = _pinned_pair(dev)
             host_totals.copy_(totals, non_blocking=True)
             flag_ready = torch.cuda.Event()
@@ -298,6 +299,7 @@ class _RenderViews(Function):
     @staticmethod
     def backward(ctx, *grads):
         lib = _abi.load()
+        st = _abi.stream()
         (means, scales, quats, viewmats, campos, intrins, background, packed, gids_sorted, tile_bins,
          final_ts, final_idx, out_img, gt, rect_ids, rect_counts) = ctx.saved_tensors
         (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride, color_shape,
@@ -329,7 +331,7 @@ class _RenderViews(Function):
                     _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(v_out_img, F32, "v_out_img"),
                     _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(out_img, F32, "out_img"),
                     1 if clamp_rgb else 0, _abi.ptr(gt, gt_dt, "gt"), 1 if gt_dt == torch.uint8 else 0,
-                    _abi.ptr(v_loss, F32, "v_loss"), _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()),
+                    _abi.ptr(v_loss, F32, "v_loss"), _abi.ptr(v_packed, F32, "v_packed"), st),
                     "sb_rasterize_rect_bwd")
         else:
           with _stage("raster_bwd"):
@@ -341,7 +343,7 @@ class _RenderViews(Function):
                 _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(out_img, F32, "out_img"),
                 1 if clamp_rgb else 0, _abi.ptr(gt, None if gt is None else gt.dtype, "gt"),
                 1 if (gt is not None and gt.dtype == torch.uint8) else 0, _abi.ptr(v_loss, F32, "v_loss"),
-                _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_bwd")
+                _abi.ptr(v_packed, F32, "v_packed"), st), "sb_rasterize_bwd")
         v_means = torch.empty(n, 3, dtype=F32, device=dev)
         v_scales = torch.empty(n, 3, dtype=F32, device=dev)
         v_quats = torch.empty(n, 4, dtype=F32, device=dev)
@@ -357,7 +359,7 @@ class _RenderViews(Function):
                 _abi.ptr(v_packed, F32, "v_packed"), _abi.ptr(v_means, F32, "v_means"),
                 _abi.ptr(v_scales, F32, "v_scales"), _abi.ptr(v_quats, F32, "v_quats"),
                 _abi.ptr(v_opac, F32, "v_opacities"), _abi.ptr(v_color, F32, "v_color_src"),
-                _abi.ptr(v_rest, F32, "v_color_rest"), _abi.stream()), "sb_views_project_bwd")
+                _abi.ptr(v_rest, F32, "v_color_rest"), st), "sb_views_project_bwd")
         return (v_means, v_scales, v_quats, v_opac, v_color, v_rest) + (None,) * (nin - 6)
 
 

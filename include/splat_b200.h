@@ -221,12 +221,16 @@ SB_API int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, c
  * which walks its own list with no block-level synchronisation: same compositing order, same images
  * and gradients as sb_rasterize_fwd / _bwd (the dropped pairs are ones those kernels skip).
  * final_idx here is the position in the rectangle's list of the last composited Gaussian (-1: none);
- * it is only meaningful to sb_rasterize_rect_bwd.  All other arguments as sb_rasterize_fwd / _bwd. */
+ * it is only meaningful to sb_rasterize_rect_bwd.  The forward is a persistent kernel (resident CTAs x
+ * SMs) whose warps pull rectangle numbers from *work_counter: one int that must be 0 on entry and is
+ * left at an unspecified value.  loss_partial here is (V, T, 8, 2): one (sum |rgb - gt|, sum (rgb - gt)^2)
+ * pair per rectangle.  All other arguments as sb_rasterize_fwd / _bwd. */
 SB_API int sb_rasterize_rect_fwd(int num_views, int n, const float* packed, const int* rect_ids,
                           const int* rect_counts, int rect_capacity, const float* background,
                           int img_h, int img_w, const int* view_has_isects, float* out_img,
                           float* final_ts, int* final_idx, float* out_alpha, int clamp_rgb_max1,
-                          const void* gt, int gt_is_u8, float* loss_partial, sb_stream_t stream);
+                          const void* gt, int gt_is_u8, float* loss_partial, int* work_counter,
+                          sb_stream_t stream);
 SB_API int sb_rasterize_rect_bwd(int num_views, int n, const float* packed, const int* rect_ids,
                           const int* rect_counts, int rect_capacity, const float* background,
                           int img_h, int img_w, const float* final_ts, const int* final_idx,

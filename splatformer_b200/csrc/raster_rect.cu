@@ -14,11 +14,16 @@
 //   * early termination is per warp (all 32 pixels saturated), not per 256-pixel tile.
 // The CTA (8 warps = the 8 rectangles of a tile) only exists for launch granularity and for the one
 // block-level sum of the fused loss.
+#include <algorithm>
+
 #include "raster_common.cuh"
 
 namespace sb {
 
-constexpr int kRectWarps = 8;     // forward: one CTA per tile (one block-level loss sum)
+#ifndef SB_RECT_FWD_WARPS
+#define SB_RECT_FWD_WARPS 8
+#endif
+constexpr int kRectWarps = SB_RECT_FWD_WARPS;     // forward: warps are independent, the CTA is launch granularity only
 constexpr int kRectWarpsB = 4;    // backward: two CTAs per tile (shared-memory budget of the slot buffers)
 
 struct RectGeom {
@@ -64,136 +69,190 @@ __device__ __forceinline__ void stage_pair_slots(PairSlots& sl, int lane, const 
   reinterpret_cast<float*>(sl.q4 + j)[h] = rC.z;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Forward: persistent warps over a queue of rectangles.
+// A rectangle's list is short (46 entries on average at the benchmark shape: 1.5 chunks), so a warp
+// that handled ONE rectangle spent more time in its dependent-load prologue (count -> ids -> records)
+// and in its store / exit epilogue than in the compositing loop.  Here the grid is sized to the machine
+// (resident CTAs per SM x SMs), every warp pulls rectangle numbers from a global counter and keeps a
+// two-deep lookahead, so that all of the next rectangle's loads are in flight while the current one
+// composites:
+//     top of rectangle k      : counter fetch for k+3;  count and first 32 ids of k+2
+//     last chunk of rectangle k: the 32 first records of k+1 (ids arrived one rectangle ago)
+// `work` is one int, zero on entry (the caller's per-step zeroed state block).
+// ------------------------------------------------------------------------------------------------
 #ifndef SB_RECT_FWD_MINB
-#define SB_RECT_FWD_MINB 4      // 64 registers, 4 CTAs/SM: measured best (3 CTAs at 80 registers: +8 %)
+#define SB_RECT_FWD_MINB 3
 #endif
+#ifndef SB_RECT_FWD_UNROLL
+#define SB_RECT_FWD_UNROLL 4
+#endif
+#define SB_PRAGMA_(x) _Pragma(#x)
+#define SB_UNROLL_(n) SB_PRAGMA_(unroll n)
+
+__device__ __forceinline__ int grab_rect(int* work, int lane) {
+  int r = 0;
+  if (lane == 0) r = atomicAdd(work, 1);
+  return __shfl_sync(0xffffffffu, r, 0);
+}
+
 __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect_fwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ rect_ids,
     const int* __restrict__ rect_counts, int cap, const float* __restrict__ background, int tiles_x,
     int tiles_y, int img_w, int img_h, const int* __restrict__ view_has_isects,
     float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx,
     float* __restrict__ out_alpha, int clamp_rgb, const void* __restrict__ gt, int gt_u8,
-    float* __restrict__ loss_partial) {
+    float* __restrict__ loss_partial, int total_rects, int* __restrict__ work) {
   __shared__ PairSlots sSlots[kRectWarps];
-  const int tile = blockIdx.x, v = blockIdx.y;
-  const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const RectGeom rg = rect_geom(tile_x, tile_y, warp, lane, img_w, img_h);
-  const size_t rect = ((size_t)v * tiles_x * tiles_y + tile) * 8 + warp;
-  const int count = __ldg(rect_counts + rect);
-  const int* ids = rect_ids + rect * cap;
-  const float4* vp = packed + (size_t)v * n * 3;
+  const int lanec = min(lane, cap - 1);
+  const int tiles = tiles_x * tiles_y;
   PairSlots& sl = sSlots[warp];
-
-  float T = 1.0f, pb = 0.f;
-  unsigned long long prg = pk2(0.f, 0.f);        // (red, green) accumulators, one FFMA2 per entry
-  int cur_idx = -1;
-  bool done = !rg.inside;
-  const unsigned long long px2 = pk2(rg.px, rg.px), py2 = pk2(rg.py, rg.py);
-
-  // registers hold the records of the NEXT 32 list entries
   const float4 nullA = make_float4(0.f, 0.f, 0.f, 0.f), nullB = make_float4(0.f, 0.f, 0.f, kNullLop);
+
+  // lookahead state: rectangle k (r0: count0, records in rA..rC), k+1 (r1: count1, id1), k+2 (r2)
+  int r0 = grab_rect(work, lane);
+  if (r0 >= total_rects) return;
+  int r1 = grab_rect(work, lane);
+  int r2 = grab_rect(work, lane);
+  int count0 = __ldg(rect_counts + r0);
+  int count1 = 0, id1 = 0;
+  if (r1 < total_rects) { count1 = __ldg(rect_counts + r1); id1 = __ldg(rect_ids + (size_t)r1 * cap + lanec); }
   float4 rA = nullA, rB = nullB, rC = nullA;
-  if (lane < count) {
-    const float4* p = vp + (size_t)__ldg(ids + lane) * 3;
+  if (lane < count0) {
+    const int v0 = (r0 >> 3) / tiles;
+    const float4* p = packed + ((size_t)v0 * n + __ldg(rect_ids + (size_t)r0 * cap + lane)) * 3;
     rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
   }
-  for (int c0 = 0; c0 < count; c0 += 32) {
-    __syncwarp();
-    stage_pair_slots(sl, lane, rA, rB, rC);
-    __syncwarp();
-    rB = nullB;
-    if (c0 + 32 + lane < count) {
-      const float4* p = vp + (size_t)__ldg(ids + c0 + 32 + lane) * 3;
-      rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
-    }
-    const int npairs = (min(32, count - c0) + 1) >> 1;
-#ifndef SB_RECT_FWD_UNROLL
-#define SB_RECT_FWD_UNROLL 4
-#endif
-#define SB_PRAGMA_(x) _Pragma(#x)
-#define SB_UNROLL_(n) SB_PRAGMA_(unroll n)
-    SB_UNROLL_(SB_RECT_FWD_UNROLL)
-    for (int j = 0; j < npairs; ++j) {
-      const float4 Q0 = sl.q0[j], Q1 = sl.q1[j], Q2 = sl.q2[j];
-      // both entries of the pair at once; every half rounds exactly like the scalar expression
-      //   pw = dx * fma(B, dy, A * dx) + (C * dy) * dy,   log2(alpha) = pw + lop
-      const unsigned long long dx2 = sub2(pk2(Q0.x, Q0.y), px2), dy2 = sub2(pk2(Q0.z, Q0.w), py2);
-      const unsigned long long t2 = fma2(pk2(Q1.z, Q1.w), dy2, mul2(pk2(Q1.x, Q1.y), dx2));
-      const unsigned long long pw2 = fma2(dx2, t2, mul2(mul2(pk2(Q2.x, Q2.y), dy2), dy2));
-      const unsigned long long e2 = add2(pw2, pk2(Q2.z, Q2.w));
-      float pw0, pw1, e0, e1;
-      upk2(pw2, pw0, pw1);
-      upk2(e2, e0, e1);
-      const float4 Q3 = sl.q3[j];
-      const float2 Q4 = *reinterpret_cast<const float2*>(sl.q4 + j);
-      {
-        const float alpha = fminf(kAlphaMax, ex2_approx(e0));
-        const bool valid = !done && (pw0 <= 0.f) && (alpha >= kAlphaMin);
-        const float next_T = T * (1.0f - alpha);
-        const bool stop = valid && (next_T <= kTMin);
-        const bool upd = valid && !stop;
-        done = done || stop;
-        const float wgt = upd ? alpha * T : 0.f;
-        prg = fma2(pk2(Q3.x, Q3.y), pk2(wgt, wgt), prg); pb = fmaf(Q4.x, wgt, pb);
-        T = upd ? next_T : T;
-        cur_idx = upd ? c0 + 2 * j : cur_idx;
-      }
-      {
-        const float alpha = fminf(kAlphaMax, ex2_approx(e1));
-        const bool valid = !done && (pw1 <= 0.f) && (alpha >= kAlphaMin);
-        const float next_T = T * (1.0f - alpha);
-        const bool stop = valid && (next_T <= kTMin);
-        const bool upd = valid && !stop;
-        done = done || stop;
-        const float wgt = upd ? alpha * T : 0.f;
-        prg = fma2(pk2(Q3.z, Q3.w), pk2(wgt, wgt), prg); pb = fmaf(Q4.y, wgt, pb);
-        T = upd ? next_T : T;
-        cur_idx = upd ? c0 + 2 * j + 1 : cur_idx;
-      }
-    }
-    if (__all_sync(0xffffffffu, done)) break;
-  }
 
-  float pr, pg;
-  upk2(prg, pr, pg);
-  float l1 = 0.f, l2 = 0.f;
-  if (rg.inside) {
-    const size_t pix = ((size_t)v * img_h + rg.py_i) * img_w + rg.px_i;
-    // upstream quirk: a view without a single intersection reports final_T = 0
-    // (alpha = 1) while its image is the plain background
-    const bool empty_view = view_has_isects ? __ldg(view_has_isects + v) == 0 : false;
-    float r = pr + T * __ldg(background), g = pg + T * __ldg(background + 1), b = pb + T * __ldg(background + 2);
-    if (clamp_rgb) { r = fminf(r, 1.0f); g = fminf(g, 1.0f); b = fminf(b, 1.0f); }   // gs_utils.py:111
-    final_ts[pix] = empty_view ? 0.f : T;
-    final_idx[pix] = cur_idx;
-    if (out_alpha) out_alpha[pix] = empty_view ? 1.f : 1.0f - T;
-    out_img[3 * pix] = r; out_img[3 * pix + 1] = g; out_img[3 * pix + 2] = b;
-    if (gt) {
-      float tr, tg, tb;
-      load_gt(gt, gt_u8, pix, tr, tg, tb);
-      const float dr = r - tr, dg = g - tg, db = b - tb;
-      l1 = fabsf(dr) + fabsf(dg) + fabsf(db);
-      l2 = dr * dr + dg * dg + db * db;
+  while (true) {
+    // ---- lookahead loads for k+2, counter fetch for k+3 ----
+    int count2 = 0, id2 = 0;
+    if (r2 < total_rects) { count2 = __ldg(rect_counts + r2); id2 = __ldg(rect_ids + (size_t)r2 * cap + lanec); }
+    const int r3 = grab_rect(work, lane);
+
+    const int tg = r0 >> 3, wt = r0 & 7;
+    const int v = tg / tiles, tile = tg - v * tiles;
+    const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
+    const RectGeom rg = rect_geom(tile_x, tile_y, wt, lane, img_w, img_h);
+    const int count = count0;
+    const int* ids = rect_ids + (size_t)r0 * cap;
+    const float4* vp = packed + (size_t)v * n * 3;
+    const float4* vp1 = packed + (size_t)((r1 >> 3) / tiles) * n * 3;      // only used when r1 is valid
+
+    float T = 1.0f, pb = 0.f;
+    unsigned long long prg = pk2(0.f, 0.f);        // (red, green) accumulators, one FFMA2 per entry
+    int cur_idx = -1;
+    bool done = !rg.inside;
+    const unsigned long long px2 = pk2(rg.px, rg.px), py2 = pk2(rg.py, rg.py);
+    bool fetched_next = false;
+
+    for (int c0 = 0; c0 < count; c0 += 32) {
+      __syncwarp();
+      stage_pair_slots(sl, lane, rA, rB, rC);
+      __syncwarp();
+      rB = nullB;
+      if (c0 + 32 < count) {
+        if (c0 + 32 + lane < count) {
+          const float4* p = vp + (size_t)__ldg(ids + c0 + 32 + lane) * 3;
+          rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
+        }
+      } else {
+        // last chunk of this rectangle: the registers now take the first chunk of the next one
+        fetched_next = true;
+        if (lane < count1) {
+          const float4* p = vp1 + (size_t)id1 * 3;
+          rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
+        }
+      }
+      const int npairs = (min(32, count - c0) + 1) >> 1;
+      SB_UNROLL_(SB_RECT_FWD_UNROLL)
+      for (int j = 0; j < npairs; ++j) {
+        const float4 Q0 = sl.q0[j], Q1 = sl.q1[j], Q2 = sl.q2[j];
+        // both entries of the pair at once; every half rounds exactly like the scalar expression
+        //   pw = dx * fma(B, dy, A * dx) + (C * dy) * dy,   log2(alpha) = pw + lop
+        const unsigned long long dx2 = sub2(pk2(Q0.x, Q0.y), px2), dy2 = sub2(pk2(Q0.z, Q0.w), py2);
+        const unsigned long long t2 = fma2(pk2(Q1.z, Q1.w), dy2, mul2(pk2(Q1.x, Q1.y), dx2));
+        const unsigned long long pw2 = fma2(dx2, t2, mul2(mul2(pk2(Q2.x, Q2.y), dy2), dy2));
+        const unsigned long long e2 = add2(pw2, pk2(Q2.z, Q2.w));
+        float pw0, pw1, e0, e1;
+        upk2(pw2, pw0, pw1);
+        upk2(e2, e0, e1);
+        const float4 Q3 = sl.q3[j];
+        const float2 Q4 = *reinterpret_cast<const float2*>(sl.q4 + j);
+        {
+          const float alpha = fminf(kAlphaMax, ex2_approx(e0));
+          const bool valid = !done && (pw0 <= 0.f) && (alpha >= kAlphaMin);
+          const float next_T = T * (1.0f - alpha);
+          const bool stop = valid && (next_T <= kTMin);
+          const bool upd = valid && !stop;
+          done = done || stop;
+          const float wgt = upd ? alpha * T : 0.f;
+          prg = fma2(pk2(Q3.x, Q3.y), pk2(wgt, wgt), prg); pb = fmaf(Q4.x, wgt, pb);
+          T = upd ? next_T : T;
+          cur_idx = upd ? c0 + 2 * j : cur_idx;
+        }
+        {
+          const float alpha = fminf(kAlphaMax, ex2_approx(e1));
+          const bool valid = !done && (pw1 <= 0.f) && (alpha >= kAlphaMin);
+          const float next_T = T * (1.0f - alpha);
+          const bool stop = valid && (next_T <= kTMin);
+          const bool upd = valid && !stop;
+          done = done || stop;
+          const float wgt = upd ? alpha * T : 0.f;
+          prg = fma2(pk2(Q3.z, Q3.w), pk2(wgt, wgt), prg); pb = fmaf(Q4.y, wgt, pb);
+          T = upd ? next_T : T;
+          cur_idx = upd ? c0 + 2 * j + 1 : cur_idx;
+        }
+      }
+      if (__all_sync(0xffffffffu, done)) break;
     }
-  }
-  if (loss_partial) {
-    // fused L1 / squared-error partial sums of the tile (train.py:275,278): one deterministic
-    // (V, T, 2) entry per CTA, summed by the caller
-    __shared__ float sRed[2][kRectWarps];
+    if (!fetched_next) {
+      // empty list, or every pixel saturated before the last chunk
+      rB = nullB;
+      if (lane < count1) {
+        const float4* p = vp1 + (size_t)id1 * 3;
+        rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
+      }
+    }
+
+    float pr, pg;
+    upk2(prg, pr, pg);
+    float l1 = 0.f, l2 = 0.f;
+    if (rg.inside) {
+      const size_t pix = ((size_t)v * img_h + rg.py_i) * img_w + rg.px_i;
+      // upstream quirk: a view without a single intersection reports final_T = 0
+      // (alpha = 1) while its image is the plain background
+      const bool empty_view = view_has_isects ? __ldg(view_has_isects + v) == 0 : false;
+      float r = pr + T * __ldg(background), g = pg + T * __ldg(background + 1), b = pb + T * __ldg(background + 2);
+      if (clamp_rgb) { r = fminf(r, 1.0f); g = fminf(g, 1.0f); b = fminf(b, 1.0f); }   // gs_utils.py:111
+      final_ts[pix] = empty_view ? 0.f : T;
+      final_idx[pix] = cur_idx;
+      if (out_alpha) out_alpha[pix] = empty_view ? 1.f : 1.0f - T;
+      out_img[3 * pix] = r; out_img[3 * pix + 1] = g; out_img[3 * pix + 2] = b;
+      if (gt) {
+        float tr, tg_, tb;
+        load_gt(gt, gt_u8, pix, tr, tg_, tb);
+        const float dr = r - tr, dg = g - tg_, db = b - tb;
+        l1 = fabsf(dr) + fabsf(dg) + fabsf(db);
+        l2 = dr * dr + dg * dg + db * db;
+      }
+    }
+    if (loss_partial) {
+      // fused L1 / squared-error partial sums (train.py:275,278): one deterministic (V, T, 8, 2) entry
+      // per rectangle, summed by the caller
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      l1 += __shfl_xor_sync(0xffffffffu, l1, o);
-      l2 += __shfl_xor_sync(0xffffffffu, l2, o);
+      for (int o = 16; o > 0; o >>= 1) {
+        l1 += __shfl_xor_sync(0xffffffffu, l1, o);
+        l2 += __shfl_xor_sync(0xffffffffu, l2, o);
+      }
+      if (lane == 0) *reinterpret_cast<float2*>(loss_partial + (size_t)r0 * 2) = make_float2(l1, l2);
     }
-    if (lane == 0) { sRed[0][warp] = l1; sRed[1][warp] = l2; }
-    __syncthreads();
-    if (threadIdx.x < 2) {
-      float t = 0.f;
-#pragma unroll
-      for (int w = 0; w < kRectWarps; ++w) t += sRed[threadIdx.x][w];
-      loss_partial[((size_t)v * tiles_x * tiles_y + tile) * 2 + threadIdx.x] = t;
-    }
+
+    if (r1 >= total_rects) break;
+    r0 = r1; count0 = count1;
+    r1 = r2; count1 = count2; id1 = id2;
+    r2 = r3;
   }
 }
 
@@ -342,20 +401,42 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rec
 
 }  // namespace sb
 
+namespace {
+// resident CTAs of a persistent kernel on the current device (cached per device)
+template <typename K>
+int persistent_grid(K kernel, int threads, int* cache) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (cache[dev] == 0) {
+    int per_sm = 0, sms = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cache[dev] = per_sm > 0 && sms > 0 ? per_sm * sms : 1;
+  }
+  return cache[dev];
+}
+}  // namespace
+
 extern "C" int sb_rasterize_rect_fwd(int num_views, int n, const float* packed, const int* rect_ids,
                                      const int* rect_counts, int rect_capacity, const float* background,
                                      int img_h, int img_w, const int* view_has_isects, float* out_img,
                                      float* final_ts, int* final_idx, float* out_alpha,
                                      int clamp_rgb_max1, const void* gt, int gt_is_u8,
-                                     float* loss_partial, sb_stream_t stream) {
-  if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || rect_capacity < 1 || (loss_partial && !gt))
+                                     float* loss_partial, int* work_counter, sb_stream_t stream) {
+  if (num_views < 1 || n < 0 || img_h < 1 || img_w < 1 || rect_capacity < 1 || (loss_partial && !gt) ||
+      !work_counter)
     return SB_ERR_BAD_ARG;
   const int tiles_x = sb::ceil_div(img_w, 16), tiles_y = sb::ceil_div(img_h, 16);
-  dim3 grid(tiles_x * tiles_y, num_views);
+  const long long total = (long long)num_views * tiles_x * tiles_y * 8;
+  if (total > 0x7fffffffLL - (1 << 24)) return SB_ERR_BAD_ARG;
+  static int grid_cache[64];
+  const int resident = persistent_grid(sb::raster_rect_fwd_kernel, sb::kRectWarps * 32, grid_cache);
+  const int grid = (int)std::min<long long>(resident, (total + sb::kRectWarps - 1) / sb::kRectWarps);
   sb::raster_rect_fwd_kernel<<<grid, sb::kRectWarps * 32, 0, (cudaStream_t)stream>>>(
       n, reinterpret_cast<const float4*>(packed), rect_ids, rect_counts, rect_capacity, background, tiles_x,
       tiles_y, img_w, img_h, view_has_isects, out_img, final_ts, final_idx, out_alpha, clamp_rgb_max1, gt,
-      gt_is_u8, loss_partial);
+      gt_is_u8, loss_partial, (int)total, work_counter);
   SB_RETURN_LAST();
 }
 

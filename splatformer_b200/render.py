@@ -184,7 +184,12 @@ class _RenderViews(Function):
         final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
         final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)
         out_alpha = None if gt is not None else torch.empty(v, img_height, img_width, dtype=F32, device=dev)
-        loss_partial = None if gt is None else torch.empty(v, num_tiles, 2, dtype=F32, device=dev)
+        # per-tile loss sums (fallback raster kernel) or per-rectangle sums (rect-list kernel)
+        loss_buf = [None]
+
+        def loss_partials(per_tile):
+            loss_buf[0] = None if gt is None else torch.empty(v, num_tiles * per_tile, 2, dtype=F32, device=dev)
+            return loss_buf[0]
 
         def project(tile_counts, tile_keys, cap):
             with _stage("project_sh_fwd"):
@@ -199,9 +204,10 @@ class _RenderViews(Function):
                     _abi.ptr(tile_counts, I32, "tile_counts"), _abi.ptr(tile_keys, torch.int64, "tile_keys"), cap,
                     st), "sb_views_project_fwd")
 
-        def raster_rect(rect_ids, rect_counts, cap, view_has):
+        def raster_rect(rect_ids, rect_counts, cap, view_has, work):
             if gt_ready is not None:
                 torch.cuda.current_stream().wait_event(gt_ready)
+            loss_partial = loss_partials(8)
             with _stage("raster_fwd"):
                 _abi.check(lib.sb_rasterize_rect_fwd(
                     v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(rect_ids, I32, "rect_ids"),
@@ -210,11 +216,13 @@ class _RenderViews(Function):
                     _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
                     _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
                     1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,
-                    _abi.ptr(loss_partial, F32, "loss_partial"), st), "sb_rasterize_rect_fwd")
+                    _abi.ptr(loss_partial, F32, "loss_partial"), _abi.ptr(work, I32, "work_counter"), st),
+                    "sb_rasterize_rect_fwd")
 
         def raster(gids_sorted, tile_bins, view_has):
             if gt_ready is not None:
                 torch.cuda.current_stream().wait_event(gt_ready)
+            loss_partial = loss_partials(1)
             with _stage("raster_fwd"):
                 _abi.check(lib.sb_rasterize_fwd(
                     v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
@@ -234,8 +242,9 @@ class _RenderViews(Function):
             # enqueued optimistically; the host then reads the overflow flag, which the GPU produced
             # BEFORE the raster kernel started -- the device never idles on this round trip.
             with _stage("zero_counts"):
-                state = torch.zeros(v * num_tiles + v + 2, dtype=I32, device=dev)
-            tile_counts, view_has, totals = state[:v * num_tiles], state[v * num_tiles:-2], state[-2:]
+                state = torch.zeros(v * num_tiles + v + 4, dtype=I32, device=dev)
+            tile_counts, view_has, totals = state[:v * num_tiles], state[v * num_tiles:-4], state[-4:-2]
+            work = state[-2:]               # rectangle queue heads of the persistent raster kernels
             tile_keys = torch.empty(v * num_tiles * cap, dtype=torch.int64, device=dev)
             gids_sorted = torch.empty(v * num_tiles * cap, dtype=I32, device=dev)
             tile_bins = torch.empty(v * num_tiles, 2, dtype=I32, device=dev)
@@ -258,7 +267,7 @@ class _RenderViews(Function):
             flag_ready = torch.cuda.Event()
             flag_ready.record()
             if use_rect:
-                raster_rect(rect_ids, rect_counts, cap, view_has)
+                raster_rect(rect_ids, rect_counts, cap, view_has, work[:1])
             else:
                 raster(gids_sorted, tile_bins, view_has)
             flag_ready.synchronize()
@@ -290,7 +299,7 @@ class _RenderViews(Function):
                               rect_ids, rect_counts)
         ctx.set_materialize_grads(False)
         if gt is not None:
-            sums = loss_partial.sum(dim=1)                       # (V, 2): sum |rgb - gt|, sum (rgb - gt)^2
+            sums = loss_buf[0].sum(dim=1)                       # (V, 2): sum |rgb - gt|, sum (rgb - gt)^2
             l1_sum, sq_sum = sums[:, 0], sums[:, 1]
             ctx.mark_non_differentiable(sq_sum, out_img)
             return l1_sum, sq_sum, out_img

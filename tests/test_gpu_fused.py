@@ -212,7 +212,8 @@ def test_fused_tile_overflow_falls_back_to_global_sort(cuda, sb_lib, monkeypatch
     monkeypatch.setattr(render, "_overflowed", {})
     l1_b, _, img_b = gs_utils.render_l1_loss(raw_b, cams, gt, return_images=True)
     assert render._overflowed, "capacity 64 must overflow on this scene"
-    assert torch.equal(img_a, img_b) and torch.equal(l1_a, l1_b)
+    # the loss sums per rectangle on the rect-list path and per tile on the fallback: same terms, different order
+    assert torch.equal(img_a, img_b) and torch.allclose(l1_a, l1_b, rtol=2e-6, atol=0)
     l1_a.sum().backward(); l1_b.sum().backward()
     for name in gs:
         H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name)

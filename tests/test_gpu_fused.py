@@ -270,3 +270,25 @@ def test_fused_loss_under_grad_scaler_magnitudes(cuda, sb_lib):
     for name in gs:
         assert torch.isfinite(raw_b[name].grad).all(), name
         assert H.rel_l2(raw_b[name].grad / 65536.0, raw_a[name].grad) <= 1e-5, name
+
+
+def test_fused_backward_twice_and_without_grad(cuda, sb_lib):
+    """The gradient records are zeroed during the forward (side stream); a second backward through a
+    retained graph must start from zero again, and a forward under no_grad allocates none."""
+    gs = synth.shell_scene(1200, 1, seed=8, scale_mult=0.3)
+    cams = {k_: v.to(cuda) for k_, v in synth.orbit_cameras(2, 80, 64).items()}
+    gt = synth.target_images(2, 64, 80, seed=5).to(cuda)
+    raw = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
+    l1, _ = gs_utils.render_l1_loss(raw, cams, gt)
+    loss = l1.mean()
+    loss.backward(retain_graph=True)
+    first = {k_: p.grad.clone() for k_, p in raw.items()}
+    for p in raw.values():
+        p.grad = None
+    loss.backward()
+    for name in gs:
+        assert torch.equal(first[name] != 0, raw[name].grad != 0), name
+        assert H.rel_l2(raw[name].grad, first[name]) <= 1e-5, name      # float atomics: order may differ
+    with torch.no_grad():
+        l1_ng, _ = gs_utils.render_l1_loss(raw, cams, gt)
+    assert torch.equal(l1_ng, l1.detach())

@@ -293,23 +293,3 @@ def test_fused_backward_twice_and_without_grad(cuda, sb_lib):
         l1_ng, _ = gs_utils.render_l1_loss(raw, cams, gt)
     assert torch.equal(l1_ng, l1.detach())
 
-
-def test_fused_segment_capacity_below_one_chunk(cuda, sb_lib, monkeypatch):
-    """Rect lists shorter than the 32-entry chunk the persistent forward prefetches per rectangle
-    (capacity 24 >= the 24 Gaussians of the scene, so no tile can overflow): same images, same gradients."""
-    from splatformer_b200 import render
-    gs = synth.shell_scene(24, 1, seed=12, scale_mult=1.5)
-    cams = {k_: v.to(cuda) for k_, v in synth.orbit_cameras(3, 72, 56).items()}
-    gt = synth.target_images(3, 56, 72, seed=2).to(cuda)
-    raw_a = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
-    raw_b = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
-    l1_a, _, img_a = gs_utils.render_l1_loss(raw_a, cams, gt, return_images=True)
-    l1_a.mean().backward()
-    monkeypatch.setattr(render, "DEFAULT_TILE_CAPACITY", 24)
-    monkeypatch.setattr(render, "_overflowed", {})
-    l1_b, _, img_b = gs_utils.render_l1_loss(raw_b, cams, gt, return_images=True)
-    l1_b.mean().backward()
-    assert not render._overflowed
-    assert torch.equal(img_a, img_b) and torch.equal(l1_a, l1_b)
-    for name in gs:
-        assert H.rel_l2(raw_b[name].grad, raw_a[name].grad) <= 1e-5, name

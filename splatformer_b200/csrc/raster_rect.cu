@@ -257,6 +257,267 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
 }
 
 // ------------------------------------------------------------------------------------------------
+// Backward, split walk (default): the two half-warps own the two 4x4 halves of the rectangle (lanes 0-15
+// the left one, lanes 16-31 the right one) and walk THEIR OWN sub-lists in lockstep.  Only 37 % of the
+// (rectangle, Gaussian) entries reach both halves, so max(|L|, |R|) is 0.72 x the entries
+// (scripts/half_rect_stats.py).  Per 32-entry chunk: every lane tests its entry against both halves
+// (the exact test of rect_mask on a 4x4 rectangle), two ballots give the sub-list positions, the record is
+// scattered into the half's pair layout back to front (slot 0 = deepest entry) together with its list
+// index, unused slots up to the longer sub-list get null records.  A step then evaluates slot s of the left
+// sub-list in lanes 0-15 and slot s of the right one in lanes 16-31; a parked slot holds two independent
+// (Gaussian, half) sums of 16 pixels each, which flush_half_slots reduces without any cross-half shuffle.
+// ------------------------------------------------------------------------------------------------
+#ifndef SB_BWD_NOSPLIT
+struct SplitLists { PairSlots half[2]; };
+
+// conservative: does {alpha >= 1/255} reach the 4x4 pixel centres starting at (ox, oy) / (ox + 4, oy)?
+__device__ __forceinline__ void half_hits(const float4& A, const float4& B, float ox, float oy, bool& hit_l,
+                                          bool& hit_r) {
+  hit_l = hit_r = false;
+  if (A.z < 0.f) return;                                      // opacity < 1/255: never visible
+  const float qa = -B.x, qb = -B.y, qc = -B.z;
+  hit_l = hit_r = true;
+  if (A.z > 1.0e37f || !(qa > 0.f) || !(qc > 0.f)) return;    // not an ellipse: no culling
+  const float qmax = (B.w + 7.994353f) * 1.0001f + 1e-3f;
+  const float rb = __fdividef(-0.5f * qb, qc), ra = __fdividef(-0.5f * qb, qa);
+  const float ly = oy - A.y, hy = ly + 3.0f;
+  const float dyc = fminf(fmaxf(0.f, ly), hy);
+  const float tc = qc * dyc * dyc, rd = ra * dyc, tb = qb * dyc;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const float lx = ox + 4.0f * j - A.x, hx = lx + 3.0f;
+    const float dxc = fminf(fmaxf(0.f, lx), hx);
+    const float dy1 = fminf(fmaxf(rb * dxc, ly), hy);
+    const float q1 = fmaf(dxc, fmaf(qb, dy1, qa * dxc), qc * dy1 * dy1);
+    const float dx2 = fminf(fmaxf(rd, lx), hx);
+    const float q2 = fmaf(dx2, fmaf(qa, dx2, tb), tc);
+    const bool hit = !(fminf(q1, q2) > qmax);                 // (a NaN keeps the pair)
+    if (j == 0) hit_l = hit; else hit_r = hit;
+  }
+}
+
+__device__ __forceinline__ void stage_slot_at(PairSlots& sl, int s, const float4& rA, const float4& rB, float lop,
+                                              float cr, float cg, float cb, int idx) {
+  const int j = s >> 1, h = s & 1;
+  float* f0 = reinterpret_cast<float*>(sl.q0 + j) + h;
+  float* f1 = reinterpret_cast<float*>(sl.q1 + j) + h;
+  float* f2 = reinterpret_cast<float*>(sl.q2 + j) + h;
+  f0[0] = rA.x; f0[2] = rA.y;
+  f1[0] = rB.x; f1[2] = rB.y;
+  f2[0] = rB.z; f2[2] = lop;
+  *reinterpret_cast<float2*>(reinterpret_cast<float*>(sl.q3 + j) + 2 * h) = make_float2(cr, cg);
+  float* f4 = reinterpret_cast<float*>(sl.q4 + j);
+  f4[h] = cb; f4[2 + h] = __int_as_float(idx);
+}
+
+// 16 parked steps x 2 halves: lane (sj, h) sums the 16 pixels of half h of step sj (one Gaussian)
+__device__ __forceinline__ void flush_half_slots(const float2* __restrict__ myW, const float4* __restrict__ myVo,
+                                                 int nslot, int lane, float own_x, float own_y, int own_g,
+                                                 float ox, float oy, float* __restrict__ vgrad) {
+  __syncwarp();
+  const int sj = lane & 15, h = lane >> 4;
+  const float2* row = myW + sj * kSlotStride + h * 16;
+  const float4* vo = myVo + h * 16;
+  float m0 = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, sxy = 0.f, syy = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    const float2 wf = row[t];
+    const float4 o = vo[t];
+    const float ix = (float)(t & 3), iy = (float)(t >> 2);
+    m0 += wf.x;
+    if (t & 3) { sx = fmaf(wf.x, ix, sx); sxx = fmaf(wf.x, ix * ix, sxx); }
+    if (t >> 2) { sy = fmaf(wf.x, iy, sy); syy = fmaf(wf.x, iy * iy, syy); }
+    if ((t & 3) && (t >> 2)) sxy = fmaf(wf.x, ix * iy, sxy);
+    cr = fmaf(wf.y, o.x, cr); cg = fmaf(wf.y, o.y, cg); cb = fmaf(wf.y, o.z, cb);
+  }
+  const float ax = own_x - (ox + (float)(4 * h)), ay = own_y - oy;
+  const float m1x = ax * m0 - sx;
+  const float m1y = ay * m0 - sy;
+  const float m2xx = ax * (m1x - sx) + sxx;
+  const float m2xy = ay * m1x - ax * sy + sxy;
+  const float m2yy = ay * (m1y - sy) + syy;
+  if (sj < nslot && own_g >= 0) {
+    float* dst = vgrad + (size_t)own_g * 12;
+    red_add_v4(dst, m1x, m1y, m2xx, m2xy);
+    red_add_v4(dst + 4, m2yy, m0, cr, cg);
+    if (cb != 0.f) atomicAdd(dst + 8, cb);
+  }
+  __syncwarp();
+}
+
+#ifndef SB_RECT_BWD_MINB
+#define SB_RECT_BWD_MINB 6      // 80 registers without spills; 36 KB of shared memory per CTA also caps it at 6
+#endif
+__global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rect_bwd_kernel(
+    int n, const float4* __restrict__ packed, const int* __restrict__ rect_ids,
+    const int* __restrict__ rect_counts, int cap, const float* __restrict__ background, int tiles_x,
+    int tiles_y, int img_w, int img_h, int clamped, const float* __restrict__ final_ts,
+    const int* __restrict__ final_idx, const float* __restrict__ v_out_img,
+    const float* __restrict__ v_out_alpha, const float* __restrict__ out_img,
+    const void* __restrict__ gt, int gt_u8, const float* __restrict__ v_loss, float* __restrict__ v_packed) {
+  __shared__ SplitLists sLists[kRectWarpsB];
+  __shared__ int sGid[kRectWarpsB][2][32];
+  __shared__ float4 sVo[kRectWarpsB][32];
+  __shared__ float2 sW[kRectWarpsB][kSlots * kSlotStride];
+  __shared__ float4 sRaw[kRectWarpsB][32][3];      // next chunk's raw records, filled by cp.async
+  constexpr int kParts = 8 / kRectWarpsB;
+  const int tile = blockIdx.x / kParts, v = blockIdx.y;
+  const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wt = warp + (blockIdx.x % kParts) * kRectWarpsB;        // rectangle index within the tile
+  const size_t rect = ((size_t)v * tiles_x * tiles_y + tile) * 8 + wt;
+  const int count = __ldg(rect_counts + rect);
+  if (count <= 0) return;
+  // pixel of this lane: lanes 0-15 the left 4x4 half of the rectangle (row-major), lanes 16-31 the right one
+  const int hh = lane >> 4;
+  const int x0 = tile_x * 16 + (wt & 1) * 8, y0 = tile_y * 16 + (wt >> 1) * 4;
+  const int px_i = x0 + 4 * hh + (lane & 3), py_i = y0 + ((lane >> 2) & 3);
+  const bool inside = px_i < img_w && py_i < img_h;
+  const float fpx = (float)px_i + 0.5f, fpy = (float)py_i + 0.5f;
+  const float ox = (float)x0 + 0.5f, oy = (float)y0 + 0.5f;
+  const int* ids = rect_ids + rect * cap;
+  const float4* vp = packed + (size_t)v * n * 3;
+  float* vgrad = v_packed + (size_t)v * n * 12;
+  PairSlots& listL = sLists[warp].half[0];
+  PairSlots& listR = sLists[warp].half[1];
+  const PairSlots& my = sLists[warp].half[hh];
+  int* sGl = sGid[warp][0];
+  int* sGr = sGid[warp][1];
+  const int* sGm = sGid[warp][hh];
+
+  float T_final = 1.f, vo_r = 0.f, vo_g = 0.f, vo_b = 0.f, vo_a = 0.f;
+  int last = -1;
+  if (inside) {
+    const size_t pix = ((size_t)v * img_h + py_i) * img_w + px_i;
+    T_final = __ldg(final_ts + pix);
+    last = __ldg(final_idx + pix);
+    if (v_out_img) {
+      vo_r = __ldg(v_out_img + 3 * pix); vo_g = __ldg(v_out_img + 3 * pix + 1); vo_b = __ldg(v_out_img + 3 * pix + 2);
+    }
+    if (v_out_alpha) vo_a = __ldg(v_out_alpha + pix);
+    if (gt) {
+      // fused L1 loss (train.py:275): d|x - gt|/dx = sign(x - gt), scaled by the upstream gradient of
+      // this view's loss term
+      const float sc = __ldg(v_loss + v);
+      float tr, tg, tb;
+      load_gt(gt, gt_u8, pix, tr, tg, tb);
+      const float dr = __ldg(out_img + 3 * pix) - tr;
+      const float dg = __ldg(out_img + 3 * pix + 1) - tg;
+      const float db = __ldg(out_img + 3 * pix + 2) - tb;
+      vo_r += dr > 0.f ? sc : (dr < 0.f ? -sc : 0.f);
+      vo_g += dg > 0.f ? sc : (dg < 0.f ? -sc : 0.f);
+      vo_b += db > 0.f ? sc : (db < 0.f ? -sc : 0.f);
+    }
+    if (out_img && clamped) {
+      // the forward stored min(rgb, 1) (gs_utils.py:111): no gradient through a clamped channel
+      if (!(__ldg(out_img + 3 * pix) < 1.0f)) vo_r = 0.f;
+      if (!(__ldg(out_img + 3 * pix + 1) < 1.0f)) vo_g = 0.f;
+      if (!(__ldg(out_img + 3 * pix + 2) < 1.0f)) vo_b = 0.f;
+    }
+  }
+  const int warp_last = __reduce_max_sync(0xffffffffu, last);
+  if (warp_last < 0) return;                      // nothing was composited in this rectangle
+  sVo[warp][lane] = make_float4(vo_r, vo_g, vo_b, 0.f);
+  const float bg_dot = __ldg(background) * vo_r + __ldg(background + 1) * vo_g + __ldg(background + 2) * vo_b;
+  // v_alpha = T * (rgb . v_out) - ra * acc,  acc = sum_{behind} fac_j (rgb_j . v_out) - T_final (v_out_alpha - bg . v_out)
+  float T = T_final;
+  float acc = -T_final * (vo_a - bg_dot);
+  int nslot = 0;
+  float own_x = 0.f, own_y = 0.f;
+  int own_g = -1;
+
+  const unsigned long long px2 = pk2(fpx, fpx), py2 = pk2(fpy, fpy);
+  const float4 nullA = make_float4(0.f, 0.f, 0.f, 0.f), nullB = make_float4(0.f, 0.f, 0.f, kNullLop);
+  // The records of the next chunk travel global -> shared by cp.async (no registers held across the
+  // walk); their ids are read two chunks ahead so that the copy's address is known when it is issued.
+  int c = warp_last >> 5;
+  float4* raw = sRaw[warp][lane];
+  auto fetch = [&](int g) {
+    const float4* p = vp + (size_t)g * 3;
+    cp_async16(raw, p); cp_async16(raw + 1, p + 1); cp_async16(raw + 2, p + 2);
+  };
+  int g_cur = 0, g_nxt = 0;
+  if (32 * c + lane <= warp_last) { g_cur = __ldg(ids + 32 * c + lane); fetch(g_cur); }
+  if (c > 0) g_nxt = __ldg(ids + 32 * (c - 1) + lane);
+  const unsigned wbase = (unsigned)__cvta_generic_to_shared(&sW[warp][lane]);
+  unsigned wcur = wbase;
+  // one step, back to front: transmittance / accumulator update and parking of (w, fac)
+  auto entry = [&](int idx, float pw, float e, float cr, float cg, float cb, float gx, float gy, int slot) {
+    const float alpha_raw = ex2_approx(e);
+    const float alpha = fminf(kAlphaMax, alpha_raw);
+    const bool valid = (idx <= last) && (pw <= 0.f) && (alpha >= kAlphaMin);
+    // a lane that skips the entry runs the same arithmetic with alpha = 0 (rcp(1) = 1: T, acc unchanged)
+    const float a = valid ? alpha : 0.f;
+    const float ra = rcp_approx(1.0f - a);
+    T *= ra;
+    const float fac = a * T;
+    const float cdot = cr * vo_r + cg * vo_g + cb * vo_b;
+    const float v_alpha = T * cdot - ra * acc;
+    acc = fmaf(fac, cdot, acc);
+    const float aw = (valid && alpha_raw <= kAlphaMax) ? alpha_raw : 0.f;
+    const float w = -aw * v_alpha;
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(wcur), "f"(w), "f"(fac) : "memory");
+    wcur += kSlotStride * (unsigned)sizeof(float2);
+    if ((lane & 15) == nslot + (slot & 1)) { own_x = gx; own_y = gy; own_g = sGm[slot]; }
+  };
+  const unsigned lt = (1u << lane) - 1u;
+  for (; c >= 0; --c) {
+    const int top = min(31, warp_last - 32 * c);
+    cp_async_wait_all();
+    float4 rA = nullA, rB = nullB, rC = nullA;
+    if (lane <= top) { rA = raw[0]; rB = raw[1]; rC = raw[2]; }
+    const int rG = g_cur;
+    bool hl = false, hr = false;
+    if (lane <= top) half_hits(rA, rB, ox, oy, hl, hr);
+    const unsigned ml = __ballot_sync(0xffffffffu, hl), mr = __ballot_sync(0xffffffffu, hr);
+    const int nl = __popc(ml), nr = __popc(mr);
+    const int npairs = (max(nl, nr) + 1) >> 1;
+    __syncwarp();
+    {
+      // hit: slot counted from the back of the sub-list; no hit: one of the unused slots gets a null record
+      const int sl_ = hl ? nl - 1 - __popc(ml & lt) : nl + __popc(~ml & lt);
+      if (sl_ < 2 * npairs) {
+        stage_slot_at(listL, sl_, rA, rB, hl ? rB.w : kNullLop, hl ? rC.x : 0.f, hl ? rC.y : 0.f, hl ? rC.z : 0.f,
+                      32 * c + lane);
+        sGl[sl_] = hl ? rG : -1;
+      }
+      const int sr_ = hr ? nr - 1 - __popc(mr & lt) : nr + __popc(~mr & lt);
+      if (sr_ < 2 * npairs) {
+        stage_slot_at(listR, sr_, rA, rB, hr ? rB.w : kNullLop, hr ? rC.x : 0.f, hr ? rC.y : 0.f, hr ? rC.z : 0.f,
+                      32 * c + lane);
+        sGr[sr_] = hr ? rG : -1;
+      }
+    }
+    __syncwarp();
+    g_cur = g_nxt;
+    if (c > 0) fetch(g_cur);
+    if (c > 1) g_nxt = __ldg(ids + 32 * (c - 2) + lane);
+    for (int j = 0; j < npairs; ++j) {
+      const float4 Q0 = my.q0[j], Q1 = my.q1[j], Q2 = my.q2[j];
+      const unsigned long long dx2 = sub2(pk2(Q0.x, Q0.y), px2), dy2 = sub2(pk2(Q0.z, Q0.w), py2);
+      const unsigned long long t2 = fma2(pk2(Q1.z, Q1.w), dy2, mul2(pk2(Q1.x, Q1.y), dx2));
+      const unsigned long long pw2 = fma2(dx2, t2, mul2(mul2(pk2(Q2.x, Q2.y), dy2), dy2));
+      const unsigned long long e2 = add2(pw2, pk2(Q2.z, Q2.w));
+      float pw0, pw1, e0, e1;
+      upk2(pw2, pw0, pw1);
+      upk2(e2, e0, e1);
+      const float4 Q3 = my.q3[j];
+      const float4 Q4 = my.q4[j];
+      entry(__float_as_int(Q4.z), pw0, e0, Q3.x, Q3.y, Q4.x, Q0.x, Q0.z, 2 * j);
+      entry(__float_as_int(Q4.w), pw1, e1, Q3.z, Q3.w, Q4.y, Q0.y, Q0.w, 2 * j + 1);
+      // two steps per iteration: the slot count stays even, one flush check per pair
+      nslot += 2;
+      if (nslot == kSlots) {
+        flush_half_slots(sW[warp], sVo[warp], kSlots, lane, own_x, own_y, own_g, ox, oy, vgrad);
+        nslot = 0;
+        wcur = wbase;
+      }
+    }
+  }
+  if (nslot) flush_half_slots(sW[warp], sVo[warp], nslot, lane, own_x, own_y, own_g, ox, oy, vgrad);
+}
+#else
+// ------------------------------------------------------------------------------------------------
 // Backward: every warp walks its rectangle's list from the last composited entry back to the front.
 // Gradient sums leave the warp through the transposed shared-memory reduction (raster_common.cuh:
 // flush_slots): 16 parked hits per flush, two red.global.add.v4.f32 + one scalar red per hit.
@@ -398,6 +659,7 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rec
   }
   if (nslot) flush_slots<true>(sW[warp], sVo[warp], nullptr, nslot, lane, own_x, own_y, own_g, rg.ox, rg.oy, vgrad);
 }
+#endif  // SB_BWD_NOSPLIT
 
 }  // namespace sb
 

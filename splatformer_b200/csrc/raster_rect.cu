@@ -12,8 +12,8 @@
 //   * no per-warp culling pass and no ballot / find-first-set loop: every list entry is a hit, the walk
 //     is a plain counted loop over consecutive shared-memory slots;
 //   * early termination is per warp (all 32 pixels saturated), not per 256-pixel tile.
-// The CTA (8 warps = the 8 rectangles of a tile) only exists for launch granularity and for the one
-// block-level sum of the fused loss.
+// The forward is persistent (warps pull rectangles from a counter, next rectangle's loads in flight); the
+// backward splits the rectangle once more into its two 4x4 halves, one per half-warp (see below).
 #include <algorithm>
 
 #include "raster_common.cuh"
@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
 }
 
 // ------------------------------------------------------------------------------------------------
-// Backward, split walk (default): the two half-warps own the two 4x4 halves of the rectangle (lanes 0-15
+// Backward, split walk: the two half-warps own the two 4x4 halves of the rectangle (lanes 0-15
 // the left one, lanes 16-31 the right one) and walk THEIR OWN sub-lists in lockstep.  Only 37 % of the
 // (rectangle, Gaussian) entries reach both halves, so max(|L|, |R|) is 0.72 x the entries
 // (scripts/half_rect_stats.py).  Per 32-entry chunk: every lane tests its entry against both halves
@@ -267,7 +267,6 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
 // sub-list in lanes 0-15 and slot s of the right one in lanes 16-31; a parked slot holds two independent
 // (Gaussian, half) sums of 16 pixels each, which flush_half_slots reduces without any cross-half shuffle.
 // ------------------------------------------------------------------------------------------------
-#ifndef SB_BWD_NOSPLIT
 struct SplitLists { PairSlots half[2]; };
 
 // conservative: does {alpha >= 1/255} reach the 4x4 pixel centres starting at (ox, oy) / (ox + 4, oy)?
@@ -516,150 +515,6 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rec
   }
   if (nslot) flush_half_slots(sW[warp], sVo[warp], nslot, lane, own_x, own_y, own_g, ox, oy, vgrad);
 }
-#else
-// ------------------------------------------------------------------------------------------------
-// Backward: every warp walks its rectangle's list from the last composited entry back to the front.
-// Gradient sums leave the warp through the transposed shared-memory reduction (raster_common.cuh:
-// flush_slots): 16 parked hits per flush, two red.global.add.v4.f32 + one scalar red per hit.
-// ------------------------------------------------------------------------------------------------
-#ifndef SB_RECT_BWD_MINB
-#define SB_RECT_BWD_MINB 7      // 72 registers: 64 forces address rematerialisation in the list walk
-#endif
-__global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rect_bwd_kernel(
-    int n, const float4* __restrict__ packed, const int* __restrict__ rect_ids,
-    const int* __restrict__ rect_counts, int cap, const float* __restrict__ background, int tiles_x,
-    int tiles_y, int img_w, int img_h, int clamped, const float* __restrict__ final_ts,
-    const int* __restrict__ final_idx, const float* __restrict__ v_out_img,
-    const float* __restrict__ v_out_alpha, const float* __restrict__ out_img,
-    const void* __restrict__ gt, int gt_u8, const float* __restrict__ v_loss, float* __restrict__ v_packed) {
-  __shared__ PairSlots sSlots[kRectWarpsB];
-  __shared__ int sGid[kRectWarpsB][32];
-  __shared__ float4 sVo[kRectWarpsB][32];
-  __shared__ float2 sW[kRectWarpsB][kSlots * kSlotStride];
-  constexpr int kParts = 8 / kRectWarpsB;
-  const int tile = blockIdx.x / kParts, v = blockIdx.y;
-  const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int wt = warp + (blockIdx.x % kParts) * kRectWarpsB;        // rectangle index within the tile
-  const RectGeom rg = rect_geom(tile_x, tile_y, wt, lane, img_w, img_h);
-  const size_t rect = ((size_t)v * tiles_x * tiles_y + tile) * 8 + wt;
-  const int count = __ldg(rect_counts + rect);
-  if (count <= 0) return;
-  const int* ids = rect_ids + rect * cap;
-  const float4* vp = packed + (size_t)v * n * 3;
-  float* vgrad = v_packed + (size_t)v * n * 12;
-  PairSlots& sl = sSlots[warp];
-  int* sG = sGid[warp];
-
-  float T_final = 1.f, vo_r = 0.f, vo_g = 0.f, vo_b = 0.f, vo_a = 0.f;
-  int last = -1;
-  if (rg.inside) {
-    const size_t pix = ((size_t)v * img_h + rg.py_i) * img_w + rg.px_i;
-    T_final = __ldg(final_ts + pix);
-    last = __ldg(final_idx + pix);
-    if (v_out_img) {
-      vo_r = __ldg(v_out_img + 3 * pix); vo_g = __ldg(v_out_img + 3 * pix + 1); vo_b = __ldg(v_out_img + 3 * pix + 2);
-    }
-    if (v_out_alpha) vo_a = __ldg(v_out_alpha + pix);
-    if (gt) {
-      // fused L1 loss (train.py:275): d|x - gt|/dx = sign(x - gt), scaled by the upstream gradient of
-      // this view's loss term
-      const float sc = __ldg(v_loss + v);
-      float tr, tg, tb;
-      load_gt(gt, gt_u8, pix, tr, tg, tb);
-      const float dr = __ldg(out_img + 3 * pix) - tr;
-      const float dg = __ldg(out_img + 3 * pix + 1) - tg;
-      const float db = __ldg(out_img + 3 * pix + 2) - tb;
-      vo_r += dr > 0.f ? sc : (dr < 0.f ? -sc : 0.f);
-      vo_g += dg > 0.f ? sc : (dg < 0.f ? -sc : 0.f);
-      vo_b += db > 0.f ? sc : (db < 0.f ? -sc : 0.f);
-    }
-    if (out_img && clamped) {
-      // the forward stored min(rgb, 1) (gs_utils.py:111): no gradient through a clamped channel
-      if (!(__ldg(out_img + 3 * pix) < 1.0f)) vo_r = 0.f;
-      if (!(__ldg(out_img + 3 * pix + 1) < 1.0f)) vo_g = 0.f;
-      if (!(__ldg(out_img + 3 * pix + 2) < 1.0f)) vo_b = 0.f;
-    }
-  }
-  const int warp_last = __reduce_max_sync(0xffffffffu, last);
-  if (warp_last < 0) return;                      // nothing was composited in this rectangle
-  sVo[warp][lane] = make_float4(vo_r, vo_g, vo_b, 0.f);
-  const float bg_dot = __ldg(background) * vo_r + __ldg(background + 1) * vo_g + __ldg(background + 2) * vo_b;
-  // v_alpha = T * (rgb . v_out) - ra * acc,  acc = sum_{behind} fac_j (rgb_j . v_out) - T_final (v_out_alpha - bg . v_out)
-  float T = T_final;
-  float acc = -T_final * (vo_a - bg_dot);
-  int nslot = 0;
-  float own_x = 0.f, own_y = 0.f;
-  int own_g = 0;
-
-  // chunk c covers list positions [32c, 32c + 32); pair j of a chunk holds positions 32c + 2j, 32c + 2j + 1
-  const unsigned long long px2 = pk2(rg.px, rg.px), py2 = pk2(rg.py, rg.py);
-  const float4 nullA = make_float4(0.f, 0.f, 0.f, 0.f), nullB = make_float4(0.f, 0.f, 0.f, kNullLop);
-  int c = warp_last >> 5;
-  float4 rA = nullA, rB = nullB, rC = nullA;
-  int rG = 0;
-  if (32 * c + lane <= warp_last) {
-    rG = __ldg(ids + 32 * c + lane);
-    const float4* p = vp + (size_t)rG * 3;
-    rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
-  }
-  // one list entry, back to front: transmittance / accumulator update and parking of (w, fac)
-  const unsigned wbase = (unsigned)__cvta_generic_to_shared(&sW[warp][lane]);
-  unsigned wcur = wbase;
-  auto entry = [&](int idx, float pw, float e, float cr, float cg, float cb, float gx, float gy, int slot) {
-    const float alpha_raw = ex2_approx(e);
-    const float alpha = fminf(kAlphaMax, alpha_raw);
-    const bool valid = (idx <= last) && (pw <= 0.f) && (alpha >= kAlphaMin);
-    if (!__any_sync(0xffffffffu, valid)) return;
-    // a lane that skips the entry runs the same arithmetic with alpha = 0 (rcp(1) = 1: T, acc unchanged)
-    const float a = valid ? alpha : 0.f;
-    const float ra = rcp_approx(1.0f - a);
-    T *= ra;
-    const float fac = a * T;
-    const float cdot = cr * vo_r + cg * vo_g + cb * vo_b;
-    const float v_alpha = T * cdot - ra * acc;
-    acc = fmaf(fac, cdot, acc);
-    const float aw = (valid && alpha_raw <= kAlphaMax) ? alpha_raw : 0.f;
-    const float w = -aw * v_alpha;
-    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(wcur), "f"(w), "f"(fac) : "memory");
-    wcur += kSlotStride * (unsigned)sizeof(float2);
-    if ((lane & 15) == nslot) { own_x = gx; own_y = gy; own_g = sG[slot]; }
-    if (++nslot == kSlots) {
-      flush_slots<true>(sW[warp], sVo[warp], nullptr, kSlots, lane, own_x, own_y, own_g, rg.ox, rg.oy, vgrad);
-      nslot = 0;
-      wcur = wbase;
-    }
-  };
-  for (; c >= 0; --c) {
-    __syncwarp();
-    stage_pair_slots(sl, lane, rA, rB, rC);
-    sG[lane] = rG;
-    __syncwarp();
-    if (c > 0) {
-      rG = __ldg(ids + 32 * (c - 1) + lane);
-      const float4* p = vp + (size_t)rG * 3;
-      rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
-    }
-    const int top = min(31, warp_last - 32 * c);
-    for (int j = top >> 1; j >= 0; --j) {
-      const float4 Q0 = sl.q0[j], Q1 = sl.q1[j], Q2 = sl.q2[j];
-      const unsigned long long dx2 = sub2(pk2(Q0.x, Q0.y), px2), dy2 = sub2(pk2(Q0.z, Q0.w), py2);
-      const unsigned long long t2 = fma2(pk2(Q1.z, Q1.w), dy2, mul2(pk2(Q1.x, Q1.y), dx2));
-      const unsigned long long pw2 = fma2(dx2, t2, mul2(mul2(pk2(Q2.x, Q2.y), dy2), dy2));
-      const unsigned long long e2 = add2(pw2, pk2(Q2.z, Q2.w));
-      float pw0, pw1, e0, e1;
-      upk2(pw2, pw0, pw1);
-      upk2(e2, e0, e1);
-      const float4 Q3 = sl.q3[j];
-      const float2 Q4 = *reinterpret_cast<const float2*>(sl.q4 + j);
-      const int idx = 32 * c + 2 * j;
-      entry(idx + 1, pw1, e1, Q3.z, Q3.w, Q4.y, Q0.y, Q0.w, 2 * j + 1);
-      entry(idx, pw0, e0, Q3.x, Q3.y, Q4.x, Q0.x, Q0.z, 2 * j);
-    }
-  }
-  if (nslot) flush_slots<true>(sW[warp], sVo[warp], nullptr, nslot, lane, own_x, own_y, own_g, rg.ox, rg.oy, vgrad);
-}
-#endif  // SB_BWD_NOSPLIT
 
 }  // namespace sb
 

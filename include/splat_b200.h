@@ -254,6 +254,8 @@ SB_API int sb_rasterize_rect_bwd(int num_views, int n, const float* packed, cons
  *   SB_FLAG_C2W_OPENGL     viewmats holds OpenGL camera-to-world matrices; the kernel forms
  *                          [R^T | -R^T T] with R <- R diag(1,-1,-1) (gs_utils.py:32-42) and takes
  *                          the camera centre from the matrix (campos may be NULL)
+ *   SB_FLAG_INTRINS_SHARED intrins is (1,4): one fx fy cx cy for all views, as SplatFormer's
+ *                          cameras are (dataset/GS.py:392-394 holds them as 0-dim tensors)
  * quats may be un-normalised in every mode (the projection normalises and the backward
  * differentiates through the normalisation, gs_utils.py:46).
  * Writes the packed raster record (V,N,12) for drawn Gaussians, depths/radii/num_tiles_hit
@@ -266,6 +268,7 @@ SB_API int sb_rasterize_rect_bwd(int num_views, int n, const float* packed, cons
 #define SB_FLAG_RAW_OPACITIES 2
 #define SB_FLAG_COLOR_SIGMOID 4
 #define SB_FLAG_C2W_OPENGL 8
+#define SB_FLAG_INTRINS_SHARED 16
 SB_API int sb_views_project_fwd(int num_views, int n, const float* means, const float* scales,
                          float glob_scale, const float* quats, const float* opacities,
                          const float* color_src, const float* color_rest, int sh_degree, int flags,

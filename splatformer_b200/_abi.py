@@ -21,6 +21,7 @@ ABI_VERSION = 2
 
 # input-convention flags of sb_views_project_fwd / _bwd (include/splat_b200.h SB_FLAG_*)
 FLAG_RAW_SCALES, FLAG_RAW_OPACITIES, FLAG_COLOR_SIGMOID, FLAG_C2W_OPENGL = 1, 2, 4, 8
+FLAG_INTRINS_SHARED = 16            # intrins is (1,4), shared by all views
 
 # name -> (restype, argtypes); mirrors include/splat_b200.h one to one
 SIGNATURES = {

@@ -256,7 +256,8 @@ extern "C" int sb_views_project_bwd(int num_views, int n, const float* means, co
       (sh_degree >= 0 && !campos && !c2w) || (sh_degree < 0 && v_color_rest))
     return SB_ERR_BAD_ARG;
   if (n == 0) return 0;
-  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0};
+  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0,
+                  (flags & sb::kFlagIntrinsShared) ? 1 : 0};
   const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
   const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsBwdRows * (k3 | 1) * sizeof(float);
   dim3 grid(sb::ceil_div(n, sb::kViewsBwdRows));

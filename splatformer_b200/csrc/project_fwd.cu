@@ -142,17 +142,19 @@ __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
       } else {
         // many tiles: claim the slots eight at a time so that the atomics' round trips overlap instead
         // of queueing behind each other (a 1M-Gaussian room scene averages 47 tiles per Gaussian)
+        // the bounding box is walked row by row with a running tile index (no integer division per tile)
         const int total = nx * (o.max_y - o.min_y);
+        size_t cur = t0 + (size_t)o.min_y * tiles_x + o.min_x;
+        int kx = 0;
         for (int b0 = 0; b0 < total; b0 += 8) {
           size_t tb[8];
           int pb[8];
 #pragma unroll
           for (int k = 0; k < 8; ++k) {
-            const int e = b0 + k;
-            if (e < total) {
-              const int ky = e / nx, kx = e - ky * nx;
-              tb[k] = t0 + (size_t)(o.min_y + ky) * tiles_x + (o.min_x + kx);
-              pb[k] = atomicAdd(tile_counts + tb[k], 1);
+            if (b0 + k < total) {
+              tb[k] = cur;
+              pb[k] = atomicAdd(tile_counts + cur, 1);
+              if (++kx == nx) { kx = 0; cur += tiles_x - nx + 1; } else { ++cur; }
             }
           }
 #pragma unroll
@@ -218,7 +220,8 @@ extern "C" int sb_views_project_fwd(int num_views, int n, const float* means, co
       ((flags & sb::kFlagColorSigmoid) && sh_degree >= 0) || (tile_counts && (!tile_keys || tile_capacity < 1)))
     return SB_ERR_BAD_ARG;
   if (n == 0) return 0;
-  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0};
+  sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0,
+                  (flags & sb::kFlagIntrinsShared) ? 1 : 0};
   const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
   const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsRows * (k3 | 1) * sizeof(float);
   dim3 grid(sb::ceil_div(n, sb::kViewsRows));

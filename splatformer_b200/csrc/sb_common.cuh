@@ -18,6 +18,7 @@ struct CamSrc {
   const float* intrins;  // (V,4) or nullptr
   float fx, fy, cx, cy;
   int c2w_opengl;        // viewmats holds OpenGL camera-to-world matrices (gs_utils.py:32-42 is done here)
+  int intr_shared;       // intrins is (1,4): one set of intrinsics for all views (dataset/GS.py:392-394)
 };
 
 __device__ __forceinline__ Cam load_cam(const CamSrc& s, int v) {
@@ -41,7 +42,7 @@ __device__ __forceinline__ Cam load_cam(const CamSrc& s, int v) {
     }
   }
   if (s.intrins) {
-    const float* k = s.intrins + 4 * v;
+    const float* k = s.intrins + (s.intr_shared ? 0 : 4 * v);
     c.fx = __ldg(k); c.fy = __ldg(k + 1); c.cx = __ldg(k + 2); c.cy = __ldg(k + 3);
   } else {
     c.fx = s.fx; c.fy = s.fy; c.cx = s.cx; c.cy = s.cy;
@@ -64,6 +65,7 @@ constexpr int kFlagRawScales = 1;      // scales are log-scales: scale = exp(raw
 constexpr int kFlagRawOpacities = 2;   // opacities are logits: opacity = sigmoid(raw)       (gs_utils.py:54)
 constexpr int kFlagColorSigmoid = 4;   // sh_degree = -1 only: colour = sigmoid(color_src)   (gs_utils.py:65)
 constexpr int kFlagC2wOpenGL = 8;      // viewmats are OpenGL camera-to-world matrices       (gs_utils.py:32-42)
+constexpr int kFlagIntrinsShared = 16; // intrins is (1,4), the same fx fy cx cy for every view (dataset/GS.py:392-394)
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 

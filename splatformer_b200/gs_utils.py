@@ -69,13 +69,14 @@ def _scalar(x) -> float:
 
 
 def _intrinsics(fx, fy, cx, cy, v: int, device) -> Tensor:
+    """(1,4) fx fy cx cy shared by all views (FLAG_INTRINS_SHARED): one small kernel, no .item()."""
     if all(isinstance(x, Tensor) for x in (fx, fy, cx, cy)):
         intr = torch.stack([fx.reshape(()), fy.reshape(()), cx.reshape(()), cy.reshape(())]).to(
             device=device, dtype=torch.float32)                                            # no .item()
     else:
         intr = torch.tensor([_scalar(fx), _scalar(fy), _scalar(cx), _scalar(cy)],
                             dtype=torch.float32).to(device, non_blocking=True)
-    return intr.reshape(1, 4).expand(v, 4).contiguous()
+    return intr.reshape(1, 4)
 
 
 def render_scene(gs_params: Dict[str, Tensor], camera_to_worlds: Tensor, cx, cy, fx, fy, width, height,
@@ -91,7 +92,7 @@ def render_scene(gs_params: Dict[str, Tensor], camera_to_worlds: Tensor, cx, cy,
     intrins = _intrinsics(fx, fy, cx, cy, v, means.device)
     rgb, alpha = render_views(means, scales, quats, opacities, dc, sh_degree, c2w, None, intrins, h, w,
                               BLOCK_WIDTH, background=background_color.to(means.device), clamp_rgb=True,
-                              color_rest=rest, flags=flags)
+                              color_rest=rest, flags=flags | _abi.FLAG_INTRINS_SHARED)
     return rgb, alpha.unsqueeze(-1)
 
 
@@ -118,7 +119,7 @@ def render_l1_loss(gs_params: Dict[str, Tensor], cameras: Dict[str, Tensor], ima
     intrins = _intrinsics(cameras["fx"], cameras["fy"], cameras["cx"], cameras["cy"], v, means.device)
     l1_sum, sq_sum, rgb = render_views(means, scales, quats, opacities, dc, sh_degree, c2w, None, intrins, h, w,
                                        BLOCK_WIDTH, background=cameras["background_color"].to(means.device),
-                                       clamp_rgb=True, color_rest=rest, flags=flags, gt=images)
+                                       clamp_rgb=True, color_rest=rest, flags=flags | _abi.FLAG_INTRINS_SHARED, gt=images)
     inv = 1.0 / (h * w * 3)
     out = (l1_sum * inv, sq_sum * inv)
     return out + (rgb,) if return_images else out

@@ -180,10 +180,15 @@ class _RenderViews(Function):
         radii = torch.empty(v, n, dtype=I32, device=dev)
         tiles_hit = torch.empty(v, n, dtype=I32, device=dev)
         num_tiles = tiles_x * tiles_y
-        out_img = torch.empty(v, img_height, img_width, 3, dtype=F32, device=dev)
-        final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
-        final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)
-        out_alpha = None if gt is not None else torch.empty(v, img_height, img_width, dtype=F32, device=dev)
+        out_img = final_ts = final_idx = out_alpha = None
+
+        def alloc_images():
+            # after the projection kernel is on its way: the host reaches the first launch sooner
+            nonlocal out_img, final_ts, final_idx, out_alpha
+            out_img = torch.empty(v, img_height, img_width, 3, dtype=F32, device=dev)
+            final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
+            final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)
+            out_alpha = None if gt is not None else torch.empty(v, img_height, img_width, dtype=F32, device=dev)
         # per-tile loss sums (fallback raster kernel) or per-rectangle sums (rect-list kernel)
         loss_buf = [None]
 
@@ -246,6 +251,8 @@ class _RenderViews(Function):
             tile_counts, view_has, totals = state[:v * num_tiles], state[v * num_tiles:-4], state[-4:-2]
             work = state[-2:]               # rectangle queue heads of the persistent raster kernels
             tile_keys = torch.empty(v * num_tiles * cap, dtype=torch.int64, device=dev)
+            project(tile_counts, tile_keys, cap)
+            alloc_images()
             gids_sorted = torch.empty(v * num_tiles * cap, dtype=I32, device=dev)
             tile_bins = torch.empty(v * num_tiles, 2, dtype=I32, device=dev)
             use_rect = block_width == 16 and USE_RECT_LISTS
@@ -253,7 +260,6 @@ class _RenderViews(Function):
                 # per-rectangle lists for the rect-list rasteriser (one warp per 8x4 rectangle)
                 rect_ids = torch.empty(v * num_tiles * 8 * cap, dtype=I32, device=dev)
                 rect_counts = torch.empty(v * num_tiles * 8, dtype=I32, device=dev)
-            project(tile_counts, tile_keys, cap)
             with _stage("sort_tiles"):
                 _abi.check(lib.sb_sort_tiles(
                     v, num_tiles, cap, _abi.ptr(tile_counts, I32, "tile_counts"),
@@ -282,6 +288,7 @@ class _RenderViews(Function):
             # very deep tiles / many tiles per Gaussian: global sort over all (tile, Gaussian) pairs
             if not cap:
                 project(None, None, 0)
+                alloc_images()
             # depth pre-order of the Gaussians, emission in that order, radix sort over the tile bits only
             with _stage("global_sort"):
                 num_intersects, _, gids_sorted, tile_bins, view_ends = utils.bin_depth_ordered(
@@ -384,7 +391,8 @@ def render_views(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor
     exp / sigmoid themselves.  color_src: (N,K,3) SH coefficients with sh_degree in 0..4 (colour =
     max(SH + 0.5, 0) as gs_utils.py:78-79; or features_dc (N,3) with color_rest = features_rest
     (N,K-1,3)), or (N,3) rgb with sh_degree = -1.  viewmats (V,3|4,4) world->camera with campos (V,3)
-    camera centres, or OpenGL camera-to-world matrices with FLAG_C2W_OPENGL; intrins (V,4) = fx, fy, cx, cy.
+    camera centres, or OpenGL camera-to-world matrices with FLAG_C2W_OPENGL; intrins (V,4) = fx, fy, cx, cy,
+    or (1,4) shared by all views with FLAG_INTRINS_SHARED.
 
     Returns rgb (V,H,W,3) and alpha (V,H,W); rgb is not clamped unless clamp_rgb=True, which folds the
     wrapper's torch.clamp(rgb, max=1) (gs_utils.py:111) into the kernels.  With gt (V,H,W,3) given it
@@ -396,6 +404,9 @@ def render_views(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor
         raise RuntimeError("render_views needs CUDA tensors (there is no CPU path)")
     if background is None:
         background = torch.ones(3, dtype=F32, device=means.device)
+    want = (1, 4) if flags & _abi.FLAG_INTRINS_SHARED else (viewmats.shape[0], 4)
+    if tuple(intrins.shape) != want:
+        raise ValueError(f"intrins must be {want}, got {tuple(intrins.shape)}")
     if campos is None and not (flags & _abi.FLAG_C2W_OPENGL):
         campos = torch.zeros(viewmats.shape[0], 3, dtype=F32, device=means.device)
     return _RenderViews.apply(means, scales, quats, opacities, color_src, color_rest, viewmats, campos, intrins,

@@ -219,6 +219,11 @@ def main() -> None:
     ap.add_argument("--cpu-views", type=int, default=3, help="views of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-packed", action="store_true",
+                    help="e2e loop uploads the scene as one packed pinned buffer (loader.pack_scene) instead of "
+                         "tensor by tensor; measured equal within box variance (DESIGN.md section 5)")
+    ap.add_argument("--e2e-submit", choices=["before_fwd", "after_fwd", "after_bwd"], default="after_bwd",
+                    help="where the e2e loop enqueues the next scene's host->device upload")
     ap.add_argument("--wrapper-steps", type=int, default=5,
                     help="timed steps of the unmodified per-view wrapper path (0 = skip)")
     ap.add_argument("--ref-views", type=int, default=2)
@@ -303,20 +308,31 @@ def main() -> None:
 
     # e2e: every step's scene comes from pinned host memory.  splatformer_b200.loader.ScenePrefetcher uploads
     # scene i+1 on a copy stream while scene i renders (every scene is still copied on every step); the
-    # upload is submitted after the step's kernels have been enqueued, so its host-side cost hides too.
+    # upload is submitted while the device is busy with the step's kernels, so its host-side cost hides too.
     from splatformer_b200 import loader as sbloader
     feeder = sbloader.ScenePrefetcher(dev)
+    if args.e2e_packed:
+        # each host scene lives in ONE pinned buffer (loader.pack_scene, done once where a DataLoader worker
+        # would collate it): the per-step upload is a single allocation + copy of the same bytes
+        host = [sbloader.pack_scene(h) for h in host]
+        h2d_bytes = host[0].blob.numel()          # what is copied per step (tensors + < 3 kB of alignment)
     e2e_feed = {"ticket": None, "steps": 0}
 
     def step_e2e(i):
         if i == 0:      # the loop's first upload is issued here, inside the timed region, and not overlapped
             e2e_feed["ticket"] = feeder.submit(host[0])
         gs_d, cams, gt_d = feeder.get(e2e_feed["ticket"])
+        if args.e2e_submit == "before_fwd" and i + 1 < e2e_feed["steps"]:
+            e2e_feed["ticket"] = feeder.submit(host[(i + 1) % NSCENE])
         raw = {k: v.requires_grad_() for k, v in gs_d.items()}
         loss = render_loss(raw, cams, gt_d)
+        # (measured: enqueueing the upload before the forward or between forward and backward is 1.5-3 %
+        #  slower than after the backward -- the host is the critical resource in those windows)
+        if args.e2e_submit == "after_fwd" and i + 1 < e2e_feed["steps"]:
+            e2e_feed["ticket"] = feeder.submit(host[(i + 1) % NSCENE])
         loss.backward()
         sync_grads(raw)
-        if i + 1 < e2e_feed["steps"]:
+        if args.e2e_submit == "after_bwd" and i + 1 < e2e_feed["steps"]:
             e2e_feed["ticket"] = feeder.submit(host[(i + 1) % NSCENE])
         return float(loss.item())          # device->host read of the step's result
 
@@ -439,7 +455,7 @@ def main() -> None:
             e2e_step = e2e_ms / args.steps
             line["e2e"] = {"value": pix_step / (e2e_step * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_step,
                            "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4,
-                           "api": "splatformer_b200.loader.ScenePrefetcher(host scenes) -> gs_utils.render_l1_loss(gs_params, "
+                           "api": "splatformer_b200.loader.ScenePrefetcher(" + ("loader.pack_scene(host scene)" if args.e2e_packed else "host scenes") + ") -> gs_utils.render_l1_loss(gs_params, "
                                   "cameras, images) + backward + loss.item()"}
         if wrapper_ms is not None:
             w_step = wrapper_ms / args.wrapper_steps

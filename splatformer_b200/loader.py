@@ -43,12 +43,80 @@ def _record(x: Any, stream: torch.cuda.Stream) -> None:
             _record(v, stream)
 
 
+class PackedScene:
+    """A scene flattened into ONE pinned host buffer (`pack_scene`): its upload is a single copy and a
+    single allocation instead of one per tensor, which is what the submit / get calls cost on the host."""
+
+    __slots__ = ("blob", "spec", "entries")
+
+    def __init__(self, blob: Tensor, spec: Any, entries):
+        self.blob, self.spec, self.entries = blob, spec, entries
+
+    @property
+    def nbytes(self) -> int:
+        return sum(e[3] for e in self.entries)
+
+
+_ALIGN = 256
+
+
+def pack_scene(item: Any, pin: bool = True) -> PackedScene:
+    """Flattens a nested dict / tuple / list of host tensors into one (pinned) uint8 buffer, every tensor
+    at a 256-byte aligned offset.  Done once per scene where it is collated (a DataLoader worker)."""
+    entries = []            # (dtype, shape, offset, nbytes)
+    tensors = []
+    total = 0
+
+    def walk(x):
+        nonlocal total
+        if isinstance(x, Tensor):
+            if x.is_cuda:
+                raise ValueError("pack_scene takes host tensors")
+            t = x.detach().contiguous()
+            nbytes = t.numel() * t.element_size()
+            entries.append((t.dtype, tuple(t.shape), total, nbytes))
+            tensors.append(t)
+            total += (nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
+            return ("t", len(entries) - 1)
+        if isinstance(x, dict):
+            return ("d", {k: walk(v) for k, v in x.items()})
+        if isinstance(x, (tuple, list)):
+            return ("l" if isinstance(x, list) else "u", [walk(v) for v in x])
+        return ("o", x)
+
+    spec = walk(item)
+    blob = torch.empty(max(total, 1), dtype=torch.uint8)
+    if pin:
+        blob = blob.pin_memory()
+    for t, (_, _, off, nbytes) in zip(tensors, entries):
+        if nbytes:
+            blob[off:off + nbytes].copy_(t.reshape(-1).view(torch.uint8))
+    return PackedScene(blob, spec, entries)
+
+
+def _unpack(spec: Any, dev_blob: Tensor, entries):
+    kind, val = spec
+    if kind == "t":
+        dtype, shape, off, nbytes = entries[val]
+        return dev_blob[off:off + nbytes].view(dtype).view(shape)
+    if kind == "d":
+        return {k: _unpack(v, dev_blob, entries) for k, v in val.items()}
+    if kind == "l":
+        return [_unpack(v, dev_blob, entries) for v in val]
+    if kind == "u":
+        return tuple(_unpack(v, dev_blob, entries) for v in val)
+    return val
+
+
 class ScenePrefetcher:
     """Uploads items (nested dicts / tuples of host tensors, ideally pinned) on a private copy stream.
 
         pf = ScenePrefetcher(device)
         ticket = pf.submit(host_scene)      # enqueue the copies, returns immediately
         scene = pf.get(ticket)              # device tensors; the current stream waits for the copies
+
+    `host_scene` may be a `PackedScene` (see `pack_scene`): one copy, and the device tensors handed out
+    are views of one device buffer.
     """
 
     def __init__(self, device: torch.device):
@@ -59,7 +127,10 @@ class ScenePrefetcher:
 
     def submit(self, item: Any):
         with torch.cuda.stream(self.stream):
-            dev_item = _upload(item, self.device)
+            if isinstance(item, PackedScene):
+                dev_item = (item, item.blob.to(self.device, non_blocking=True))
+            else:
+                dev_item = _upload(item, self.device)
             ready = torch.cuda.Event()
             ready.record(self.stream)
         return dev_item, ready
@@ -68,6 +139,10 @@ class ScenePrefetcher:
         dev_item, ready = ticket
         cur = torch.cuda.current_stream(self.device)
         cur.wait_event(ready)
+        if isinstance(dev_item, tuple) and len(dev_item) == 2 and isinstance(dev_item[0], PackedScene):
+            packed, dev_blob = dev_item
+            dev_blob.record_stream(cur)     # allocated on the copy stream; the views share its storage
+            return _unpack(packed.spec, dev_blob, packed.entries)
         _record(dev_item, cur)              # the tensors were allocated on the copy stream
         return dev_item
 

@@ -168,61 +168,34 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
   // ---- rect lists: for each of the tile's eight 8x4 rectangles, the depth-ordered ids of the Gaussians
   // whose visible region reaches it (raster_common.cuh: rect_mask), compacted stably per rectangle into
   // rect_ids[(tile * 8 + r) * cap + ...]; the rect-list rasteriser gives every rectangle to one warp.
-  // Entry i belongs to slot (i / 256, warp): phase A computes every entry's 8-bit mask and the per-slot
-  // counts, one warp per rectangle then scans the slot counts, phase C writes the ids.  The bucket
-  // table s_end is free by now and holds the masks (cap bytes) and the slot counts (cap bytes).
+  // Phase A: every entry's 8-bit rectangle mask into shared memory (the bucket table s_end is free by now).
+  // Phase B: warp r owns rectangle r and walks the masks in list order, 32 entries per step: one ballot on
+  // bit r, the set lanes store their ids behind the warp's running offset -- stable, no counts to scan.
   unsigned char* s_mask = reinterpret_cast<unsigned char*>(s_end);
-  int* s_cnt = s_end + (cap >> 2);                 // [slot][8], slot = chunk * 8 + warp
   const int v = blockIdx.x / tiles_per_view, tile = blockIdx.x - v * tiles_per_view;
   const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
   const float4* vp = packed + (size_t)v * n * 3;
-  int* out = rect_ids + (size_t)blockIdx.x * 8 * cap;
-  const int nchunks = (len + kSortBlock - 1) / kSortBlock;
   __syncthreads();                                 // everyone is done with s_end as the bucket table
-  for (int c = 0; c < nchunks; ++c) {
-    const int i = c * kSortBlock + threadIdx.x;
-    unsigned mask = 0u;
-    if (i < len) {
-      const float4* rec = vp + (size_t)(unsigned)(s_keys[i] & 0xffffffffull) * 3;
-      mask = rect_mask(__ldg(rec), __ldg(rec + 1), tile_x, tile_y);
-      s_mask[i] = (unsigned char)mask;
-    }
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      const unsigned bal = __ballot_sync(0xffffffffu, (mask >> r) & 1u);
-      if (lane == r) s_cnt[(c * 8 + warp) * 8 + r] = __popc(bal);
-    }
+  for (int i = threadIdx.x; i < len; i += kSortBlock) {
+    const float4* rec = vp + (size_t)(unsigned)(s_keys[i] & 0xffffffffull) * 3;
+    s_mask[i] = (unsigned char)rect_mask(__ldg(rec), __ldg(rec + 1), tile_x, tile_y);
   }
   __syncthreads();
   {
-    // warp r: exclusive scan of rectangle r's slot counts, in slot order
-    const int r = warp, nslots = nchunks * 8;
-    int carry = 0;
-    for (int j0 = 0; j0 < nslots; j0 += 32) {
-      const int j = j0 + lane;
-      const int cnt = j < nslots ? s_cnt[j * 8 + r] : 0;
-      int x = cnt;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int y = __shfl_up_sync(0xffffffffu, x, o);
-        if (lane >= o) x += y;
-      }
-      if (j < nslots) s_cnt[j * 8 + r] = carry + x - cnt;
-      carry += __shfl_sync(0xffffffffu, x, 31);
+    const int r = warp;                            // kSortBlock / 32 == 8 rectangles
+    int* out = rect_ids + ((size_t)blockIdx.x * 8 + r) * cap;
+    const unsigned lt = (1u << lane) - 1u;
+    int off = 0;
+    static_assert(kSortBlock == 8 * 32, "one warp per rectangle");
+#pragma unroll 4
+    for (int i0 = 0; i0 < len; i0 += 32) {
+      const int i = i0 + lane;
+      const bool hit = i < len && ((s_mask[i] >> r) & 1u);
+      const unsigned bal = __ballot_sync(0xffffffffu, hit);
+      if (hit) out[off + __popc(bal & lt)] = (int)(unsigned)(s_keys[i] & 0xffffffffull);
+      off += __popc(bal);
     }
-    if (lane == 0) rect_counts[(size_t)blockIdx.x * 8 + r] = carry;
-  }
-  __syncthreads();
-  for (int c = 0; c < nchunks; ++c) {
-    const int i = c * kSortBlock + threadIdx.x;
-    const unsigned mask = i < len ? s_mask[i] : 0u;
-    const int g = i < len ? (int)(unsigned)(s_keys[i] & 0xffffffffull) : 0;
-    const int* pre = s_cnt + (c * 8 + warp) * 8;
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      const unsigned bal = __ballot_sync(0xffffffffu, (mask >> r) & 1u);
-      if ((mask >> r) & 1u) out[(size_t)r * cap + pre[r] + __popc(bal & ((1u << lane) - 1u))] = g;
-    }
+    if (lane == 0) rect_counts[(size_t)blockIdx.x * 8 + r] = off;
   }
 }
 

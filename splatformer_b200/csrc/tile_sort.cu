@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
   extern __shared__ unsigned long long s_keys[];
   int* s_end = reinterpret_cast<int*>(s_keys + cap);
   __shared__ unsigned s_min, s_max;
-  __shared__ int s_warp[kSortBlock / 32], s_carry, s_overflow;
+  __shared__ int s_warp[kSortBlock / 32], s_overflow;
   const int count = __ldg(counts + blockIdx.x);
   const int len = min(count, cap);
   const int2 range = make_int2(blockIdx.x * cap, blockIdx.x * cap + len);       // V*T*cap < 2^31 (host checks)
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
   }
   lo = __reduce_min_sync(0xffffffffu, lo);
   hi = __reduce_max_sync(0xffffffffu, hi);
-  if (threadIdx.x == 0) { s_min = 0xffffffffu; s_max = 0u; s_carry = 0; s_overflow = 0; }
+  if (threadIdx.x == 0) { s_min = 0xffffffffu; s_max = 0u; s_overflow = 0; }
   for (int i = threadIdx.x; i < nb; i += kSortBlock) s_end[i] = 0;
   __syncthreads();
   if (lane == 0) { atomicMin(&s_min, lo); atomicMax(&s_max, hi); }
@@ -112,12 +112,21 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
   // pass 2: histogram
   for (int i = threadIdx.x; i < len; i += kSortBlock) atomicAdd(&s_end[bucket_of(__ldg(src + i))], 1);
   __syncthreads();
-  // exclusive scan of the histogram (s_end[b] becomes the start of bucket b and is then advanced to its end)
-  for (int base = 0; base < nb; base += kSortBlock) {
-    const bool in = base + (int)threadIdx.x < nb;
-    const int c = in ? s_end[base + threadIdx.x] : 0;
-    if (c > kBucketMax) s_overflow = 1;
-    int x = c;
+  // exclusive scan of the histogram (s_end[b] becomes the start of bucket b and is then advanced to its end):
+  // every thread sums its own nb / 256 consecutive buckets, one block-wide scan of the 256 partial sums,
+  // then the thread lays its buckets' starts down -- two barriers in all, whatever nb is
+  {
+    const int per = nb >= kSortBlock ? nb / kSortBlock : 1;     // nb is a power of two >= 64
+    const int b0 = threadIdx.x * per;
+    int sum = 0;
+    if (b0 < nb) {
+      for (int j = 0; j < per; ++j) {
+        const int c = s_end[b0 + j];
+        if (c > kBucketMax) s_overflow = 1;
+        sum += c;
+      }
+    }
+    int x = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const int y = __shfl_up_sync(0xffffffffu, x, o);
@@ -125,13 +134,15 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
     }
     if (lane == 31) s_warp[warp] = x;
     __syncthreads();
-    int wsum = 0;
-    for (int w = 0; w < warp; ++w) wsum += s_warp[w];
-    const int carry = s_carry;
-    const int incl = carry + wsum + x;
-    if (in) s_end[base + threadIdx.x] = incl - c;
-    __syncthreads();
-    if (threadIdx.x == kSortBlock - 1) s_carry = incl;
+    int start = x - sum;
+    for (int w = 0; w < warp; ++w) start += s_warp[w];
+    if (b0 < nb) {
+      for (int j = 0; j < per; ++j) {
+        const int c = s_end[b0 + j];
+        s_end[b0 + j] = start;
+        start += c;
+      }
+    }
     __syncthreads();
   }
   // pass 3: scatter into buckets

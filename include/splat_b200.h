@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define SB_ABI_VERSION 2
+#define SB_ABI_VERSION 3
 #define SB_ERR_BAD_ARG (-1)
 #define SB_ERR_TEMP_TOO_SMALL (-2)
 
@@ -256,8 +256,15 @@ SB_API int sb_rasterize_rect_bwd(int num_views, int n, const float* packed, cons
  *                          the camera centre from the matrix (campos may be NULL)
  *   SB_FLAG_INTRINS_SHARED intrins is (1,4): one fx fy cx cy for all views, as SplatFormer's
  *                          cameras are (dataset/GS.py:392-394 holds them as 0-dim tensors)
- * quats may be un-normalised in every mode (the projection normalises and the backward
- * differentiates through the normalisation, gs_utils.py:46).
+ *   SB_FLAG_RAW_QUATS      quats are raw: the kernel does the wrapper's q / |q| and replaces a
+ *                          quaternion that does not come out unit (zero, NaN, infinite) by
+ *                          (0,0,0,1), which then receives no gradient          (gs_utils.py:46-51)
+ * quats may be un-normalised in every mode (the projection normalises -- a second time with
+ * SB_FLAG_RAW_QUATS, exactly as gsplat does with the wrapper's output -- and the backward
+ * differentiates through the normalisations).
+ * stats (backward, may be NULL): two ints the caller zero-fills; the kernel adds the number of
+ * (view, Gaussian) records it scanned to [0] and the number with a non-zero gradient (the ones whose
+ * VJP it evaluated) to [1].
  * Writes the packed raster record (V,N,12) for drawn Gaussians, depths/radii/num_tiles_hit
  * (V,N) for all.  The backward consumes the packed gradient record of sb_rasterize_bwd and
  * writes the per-Gaussian sums over views: v_means (N,3) v_scales (N,3) v_quats (N,4)
@@ -269,6 +276,7 @@ SB_API int sb_rasterize_rect_bwd(int num_views, int n, const float* packed, cons
 #define SB_FLAG_COLOR_SIGMOID 4
 #define SB_FLAG_C2W_OPENGL 8
 #define SB_FLAG_INTRINS_SHARED 16
+#define SB_FLAG_RAW_QUATS 32
 SB_API int sb_views_project_fwd(int num_views, int n, const float* means, const float* scales,
                          float glob_scale, const float* quats, const float* opacities,
                          const float* color_src, const float* color_rest, int sh_degree, int flags,
@@ -283,7 +291,7 @@ SB_API int sb_views_project_bwd(int num_views, int n, const float* means, const 
                          float fy, float cx, float cy, const float* campos, int img_h, int img_w,
                          int block_width, float clip_thresh, const float* packed,
                          const float* v_packed, float* v_means, float* v_scales, float* v_quats,
-                         float* v_opacities, float* v_color_src, float* v_color_rest,
+                         float* v_opacities, float* v_color_src, float* v_color_rest, int* stats,
                          sb_stream_t stream);
 
 #ifdef __cplusplus

@@ -344,6 +344,34 @@ def bin_and_sort_gaussians(num_points: int, num_intersects: int, xys: Tensor, de
     return isect_ids, gaussian_ids, isect_ids_sorted, gaussian_ids_sorted, tile_bins
 
 
+def tile_lists(xys: Tensor, depths: Tensor, radii: Tensor, tile_bounds, block_width: int, tiles):
+    """The sorted Gaussian-id list of each tile in `tiles`, computed tile by tile instead of through the
+    global sort: the Gaussians whose tile bbox (A.3) contains the tile, ordered by (depth bits, Gaussian
+    id) -- which is what the stable sort of A.4 leaves in that tile's bin (keys of one tile differ only in
+    the depth bits; ties keep emission order = ascending id).  For frames whose full key array is too
+    large for this CPU code (BASELINE configs 4 and 5); tests/test_oracle_crosscheck.py checks it against
+    bin_and_sort_gaussians.  Returns (gaussian_ids_sorted, tile_bins) in the layout rasterize_forward
+    takes, holding only the requested tiles."""
+    tiles_x, tiles_y = int(tile_bounds[0]), int(tile_bounds[1])
+    xf = xys.detach().float()
+    min_x, max_x, min_y, max_y = _tile_bbox(xf[:, 0], xf[:, 1], radii.float(), tiles_x, tiles_y, block_width)
+    hit = radii > 0
+    depth_bits = depths.detach().float().contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+    bins = torch.zeros(tiles_x * tiles_y, 2, dtype=torch.int32)
+    parts, off = [], 0
+    for t in sorted(set(int(t) for t in tiles)):
+        ty, tx = divmod(t, tiles_x)
+        ids = torch.nonzero(hit & (min_x <= tx) & (tx < max_x) & (min_y <= ty) & (ty < max_y)).flatten()
+        if ids.numel() == 0:
+            continue
+        order = torch.sort((depth_bits[ids] << 32) | ids, stable=True).indices
+        parts.append(ids[order].to(torch.int32))
+        bins[t, 0], bins[t, 1] = off, off + ids.numel()
+        off += ids.numel()
+    gids = torch.cat(parts) if parts else torch.zeros(0, dtype=torch.int32)
+    return gids, bins
+
+
 # ----------------------------------------------------------------------------
 # A.5 rasterise forward (autograd supplies A.6)
 # ----------------------------------------------------------------------------
@@ -386,11 +414,14 @@ def _composite_tile(dx: Tensor, dy: Tensor, conic: Tensor, opac: Tensor, rgb: Te
 
 def rasterize_forward(xys: Tensor, conics: Tensor, colors: Tensor, opacity: Tensor,
                       gaussian_ids_sorted: Tensor, tile_bins: Tensor, img_height: int,
-                      img_width: int, block_width: int, background: Tensor):
+                      img_width: int, block_width: int, background: Tensor, tiles=None):
     """Per-tile front-to-back compositing (A.5).  Differentiable in xys, conics,
     colors, opacity.  Returns out_img (H,W,3), final_Ts (H,W), final_idx (H,W) int32
     and the per-pixel decision margin (H,W) used by tests to set aside pixels whose
-    alpha>=1/255 / T<=1e-4 / 0.999-clamp decision lies within rounding noise."""
+    alpha>=1/255 / T<=1e-4 / 0.999-clamp decision lies within rounding noise.
+    `tiles` (iterable of tile indices) restricts the compositing to those tiles -- tiles are
+    independent, so a subset of a frame too large for this CPU code is still an exact check of
+    the pixels it covers; all other pixels are left at T = 1 (background)."""
     dt = colors.dtype
     tiles_x = (img_width + block_width - 1) // block_width
     tiles_y = (img_height + block_width - 1) // block_width
@@ -402,7 +433,11 @@ def rasterize_forward(xys: Tensor, conics: Tensor, colors: Tensor, opacity: Tens
     margin_img = torch.full((img_height, img_width), 1e9, dtype=dt)
     img_parts, t_parts = [], []
     bins = tile_bins.to(torch.int64)
-    for t in torch.nonzero(bins[:, 1] > bins[:, 0]).flatten().tolist():
+    occupied = torch.nonzero(bins[:, 1] > bins[:, 0]).flatten().tolist()
+    if tiles is not None:
+        wanted = set(int(t) for t in tiles)
+        occupied = [t for t in occupied if t in wanted]
+    for t in occupied:
         start, end = int(bins[t, 0]), int(bins[t, 1])
         ids = gaussian_ids_sorted[start:end].to(torch.int64)
         ty, tx = divmod(t, tiles_x)
@@ -440,8 +475,8 @@ def rasterize_forward(xys: Tensor, conics: Tensor, colors: Tensor, opacity: Tens
 def rasterize_gaussians(xys: Tensor, depths: Tensor, radii: Tensor, conics: Tensor,
                         num_tiles_hit: Tensor, colors: Tensor, opacity: Tensor, img_height: int,
                         img_width: int, block_width: int, background: Optional[Tensor] = None,
-                        return_alpha: bool = False, return_aux: bool = False):
-    """gsplat.rasterize_gaussians (call site gs_utils.py:96-109)."""
+                        return_alpha: bool = False, return_aux: bool = False, tiles=None):
+    """gsplat.rasterize_gaussians (call site gs_utils.py:96-109).  `tiles`: see rasterize_forward."""
     assert 2 <= block_width <= 16, "block_width must be between 2 and 16"
     if colors.dtype == torch.uint8:
         colors = colors.float() / 255
@@ -467,11 +502,16 @@ def rasterize_gaussians(xys: Tensor, depths: Tensor, radii: Tensor, conics: Tens
                    isect_ids_sorted=torch.zeros(0, dtype=torch.int64),
                    tile_bins=torch.zeros(tiles_x * tiles_y, 2, dtype=torch.int32))
     else:
-        _, _, isect_sorted, gids_sorted, tile_bins = bin_and_sort_gaussians(
-            num_points, num_intersects, xys, depths, radii, cum, (tiles_x, tiles_y, 1), block_width)
+        if tiles is None:
+            _, _, isect_sorted, gids_sorted, tile_bins = bin_and_sort_gaussians(
+                num_points, num_intersects, xys, depths, radii, cum, (tiles_x, tiles_y, 1), block_width)
+        else:
+            # only the requested tiles' lists (same lists, no global key array): see tile_lists
+            isect_sorted = None
+            gids_sorted, tile_bins = tile_lists(xys, depths, radii, (tiles_x, tiles_y, 1), block_width, tiles)
         out_img, final_ts, final_idx, margin = rasterize_forward(
             xys, conics, colors, opacity, gids_sorted, tile_bins, img_height, img_width,
-            block_width, background)
+            block_width, background, tiles=tiles)
         aux = dict(num_intersects=num_intersects, final_idx=final_idx, margin=margin,
                    gaussian_ids_sorted=gids_sorted, isect_ids_sorted=isect_sorted,
                    tile_bins=tile_bins)
@@ -489,24 +529,51 @@ def viewmat_from_c2w(camera_to_world: Tensor) -> Tensor:
     """OpenGL camera-to-world (3x4 or 4x4) -> OpenCV world-to-camera 4x4
     (gs_utils.py:32-42: R <- R diag(1,-1,-1); viewmat = [R^T | -R^T T])."""
     rot = camera_to_world[:3, :3] * torch.tensor([1.0, -1.0, -1.0], dtype=camera_to_world.dtype)[None, :]
-    trans = camera_to_world[:3, 3:4]
+    trans = camera_to_world[:3, 3]
     vm = torch.eye(4, dtype=camera_to_world.dtype)
     vm[:3, :3] = rot.T
-    vm[:3, 3:4] = -rot.T @ trans
+    # -R^T T with every product and sum rounded separately, left to right (arithmetic contract of this
+    # file: no matmul -- a BLAS gemv may fuse or reorder); the CUDA kernels repeat exactly this
+    for i in range(3):
+        vm[i, 3] = -(rot[0, i] * trans[0] + rot[1, i] * trans[1] + rot[2, i] * trans[2])
     return vm
 
 
+def wrapper_normalise_quats(q: Tensor) -> Tensor:
+    """gs_utils.py:46-51, literally: quats = q / norm(q); rows whose result is not unit -- one-sided test
+    (norm - 1) < 1e-6, so zero, NaN and infinite quaternions -- are replaced by (0, 0, 0, 1).  The norm
+    is the separately rounded left-to-right sum of squares and a correctly rounded sqrt.  Replaced rows
+    receive no gradient."""
+    def sumsq(t):
+        return t[:, 0] * t[:, 0] + t[:, 1] * t[:, 1] + t[:, 2] * t[:, 2] + t[:, 3] * t[:, 3]
+    qd = q.detach()
+    n = _sqrt(sumsq(qd))
+    n1 = _sqrt(sumsq(qd / n[:, None]))
+    good = (n1 - 1.0) < 1e-6                                       # False for NaN
+    # double-where: the replaced rows go through the differentiable branch as (1,0,0,0), so that their
+    # masked-out gradient is an exact zero instead of 0 * inf
+    q_safe = torch.where(good[:, None], q, torch.tensor([1.0, 0.0, 0.0, 0.0], dtype=q.dtype).expand_as(q))
+    unit = q_safe / _sqrt(sumsq(q_safe))[:, None]
+    subst = torch.tensor([0.0, 0.0, 0.0, 1.0], dtype=q.dtype).expand_as(q)
+    return torch.where(good[:, None], unit, subst)
+
+
 def render_view(gs_params: dict, camera_to_world: Tensor, cx, cy, fx, fy, width, height,
-                background_color: Tensor, block_width: int = 16, return_aux: bool = False):
+                background_color: Tensor, block_width: int = 16, return_aux: bool = False,
+                exp=torch.exp, sigmoid=torch.sigmoid, tiles=None):
     """The logic of rasterize_gaussians_to_singleimg (gs_utils.py:29-114) on top of
-    this oracle: activations, colour path selection, three gsplat calls, clamps."""
+    this oracle: activations, colour path selection, three gsplat calls, clamps.
+    `exp` / `sigmoid`: the activation implementations (gs_utils.py:45,54,65).  The reference runs
+    torch.exp / torch.sigmoid ON THE GPU; a parity test that wants the oracle to see the very bits the
+    reference's wrapper would hand to gsplat passes differentiable stand-ins that evaluate there
+    (tests/helpers.py: gpu_exp, gpu_sigmoid).  `tiles`: composite only these tiles (rasterize_forward)."""
     gp = {k: (v.float() if v.dtype == torch.half else v) for k, v in gs_params.items()}
     viewmat = viewmat_from_c2w(camera_to_world)
     means = gp["means"]
-    scales = torch.exp(gp["scales"])
-    quats = gp["quats"] / torch.norm(gp["quats"], dim=-1, keepdim=True)
+    scales = exp(gp["scales"])
+    quats = wrapper_normalise_quats(gp["quats"])
     if "opacities" in gp:
-        opacities = torch.sigmoid(gp["opacities"])
+        opacities = sigmoid(gp["opacities"])
     elif "opacities_sigmoid" in gp:
         opacities = gp["opacities_sigmoid"]
     else:
@@ -517,10 +584,16 @@ def render_view(gs_params: dict, camera_to_world: Tensor, cx, cy, fx, fy, width,
         coeffs = gp["features_dc"].unsqueeze(1)
     degree = int(math.sqrt(coeffs.shape[1]) - 1)
     if degree == 0:
-        rgbs = torch.sigmoid(coeffs[:, 0, :])
+        rgbs = sigmoid(coeffs[:, 0, :])
     else:
         dirs = means.detach() - camera_to_world.detach()[:3, 3]
-        dirs = dirs / dirs.norm(dim=-1, keepdim=True)
+        norm = dirs.norm(dim=-1, keepdim=True)
+        # gs_utils.py:72-76: a mean ON the camera centre gets a random unit direction upstream.  Such a
+        # Gaussian has depth 0 and is culled by the near plane, so the direction never reaches a pixel; a
+        # fixed one keeps the oracle deterministic (and its autograd free of 0 * NaN).
+        at_centre = norm == 0
+        dirs = torch.where(at_centre, torch.tensor([0.0, 0.0, 1.0], dtype=dirs.dtype).expand_as(dirs),
+                           dirs / torch.where(at_centre, torch.ones_like(norm), norm))
         rgbs = torch.clamp(spherical_harmonics(degree, dirs, coeffs) + 0.5, min=0.0)
     h, w = int(height), int(width)
     xys, depths, radii, conics, comp, num_tiles_hit, cov3d = project_gaussians(
@@ -528,7 +601,7 @@ def render_view(gs_params: dict, camera_to_world: Tensor, cx, cy, fx, fy, width,
         float(cy), h, w, block_width)
     res = rasterize_gaussians(xys, depths, radii, conics, num_tiles_hit, rgbs, opacities, h, w,
                               block_width, background=background_color.to(means.dtype),
-                              return_alpha=True, return_aux=return_aux)
+                              return_alpha=True, return_aux=return_aux, tiles=tiles)
     rgb = torch.clamp(res[0], max=1.0)
     alpha = res[1].unsqueeze(-1)
     if return_aux:

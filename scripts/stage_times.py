@@ -24,6 +24,6 @@ torch.cuda.synchronize()
 with render.profile_stages() as t:
     for _ in range(3): step()
 tot, cnt = t.totals_ms(), t.counts()
-print(name, "isects", render.last_num_intersects(), "overflowed", render._overflowed)
+print(name, "isects", render.last_num_intersects(), "overflowed", render._default_plan.overflowed)
 for k in tot: print(f"  {k:16s} {tot[k]/3:9.3f} ms/step ({cnt[k]//3} launches)")
 print("  sum", sum(tot.values()) / 3)

@@ -17,11 +17,12 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "lib
 _lib: Optional[ctypes.CDLL] = None
 
 P, I, F, S = c_void_p, c_int, c_float, c_size_t
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 # input-convention flags of sb_views_project_fwd / _bwd (include/splat_b200.h SB_FLAG_*)
 FLAG_RAW_SCALES, FLAG_RAW_OPACITIES, FLAG_COLOR_SIGMOID, FLAG_C2W_OPENGL = 1, 2, 4, 8
 FLAG_INTRINS_SHARED = 16            # intrins is (1,4), shared by all views
+FLAG_RAW_QUATS = 32                 # quats are raw: wrapper's q / |q| and (0,0,0,1) substitution in-kernel
 
 # name -> (restype, argtypes); mirrors include/splat_b200.h one to one
 SIGNATURES = {
@@ -57,7 +58,7 @@ SIGNATURES = {
     "sb_rasterize_rect_fwd": (I, [I, I, P, P, P, I, P, I, I, P, P, P, P, P, I, P, I, P, P, P]),
     "sb_rasterize_rect_bwd": (I, [I, I, P, P, P, I, P, I, I, P, P, P, P, P, I, P, I, P, P, P]),
     "sb_views_project_bwd": (I, [I, I, P, P, F, P, I, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P, P, P, P,
-                                 P, P]),
+                                 P, P, P]),
 }
 
 # number of ABI calls that enqueued device work since import (bench.py reports it as gpu_launches)

@@ -100,7 +100,8 @@ __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
   float s[3] = {__ldg(scales + 3 * g), __ldg(scales + 3 * g + 1), __ldg(scales + 3 * g + 2)};
   if (flags & kFlagRawScales) { s[0] = expf(s[0]); s[1] = expf(s[1]); s[2] = expf(s[2]); }
   const float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
-  const float q[4] = {q4.x, q4.y, q4.z, q4.w};
+  float q[4] = {q4.x, q4.y, q4.z, q4.w};
+  if (flags & kFlagRawQuats) wrapper_normalise_quat(q);      // gs_utils.py:46-51
   float op = __ldg(opacities + g);
   if (flags & kFlagRawOpacities) op = sigmoidf_(op);
   // blocks start at different views so that, at any moment, the per-tile count reductions of the

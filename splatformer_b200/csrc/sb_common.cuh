@@ -66,6 +66,7 @@ constexpr int kFlagRawOpacities = 2;   // opacities are logits: opacity = sigmoi
 constexpr int kFlagColorSigmoid = 4;   // sh_degree = -1 only: colour = sigmoid(color_src)   (gs_utils.py:65)
 constexpr int kFlagC2wOpenGL = 8;      // viewmats are OpenGL camera-to-world matrices       (gs_utils.py:32-42)
 constexpr int kFlagIntrinsShared = 16; // intrins is (1,4), the same fx fy cx cy for every view (dataset/GS.py:392-394)
+constexpr int kFlagRawQuats = 32;      // quats are raw: q / |q|, degenerate ones -> (0,0,0,1)  (gs_utils.py:46-51)
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 

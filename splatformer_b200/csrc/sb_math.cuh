@@ -116,6 +116,20 @@ SB_HD void tile_bbox(float px, float py, float radius, int tiles_x, int tiles_y,
 
 SB_HD bool sb_finite(float v) { return (v - v) == 0.0f; }
 
+// Wrapper-level quaternion normalisation, literally /root/reference/utils/gs_utils.py:46-51:
+//   quats = q / norm(q);  mask = (norm(quats) - 1) < 1e-6;  quats[~mask] = (0, 0, 0, 1)
+// (a zero, NaN or infinite quaternion fails the one-sided test and is replaced).  The projection then
+// normalises once more, as gsplat.project_gaussians does with the wrapper's output.  Returns the norm
+// of the raw quaternion, or 0 when the substitution happened (no gradient flows to such a quaternion).
+SB_HD float wrapper_normalise_quat(float* q) {
+  const float n = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  const float a = q[0] / n, b = q[1] / n, c = q[2] / n, d = q[3] / n;
+  const float n1 = sqrtf(a * a + b * b + c * c + d * d);
+  if (!(n1 - 1.0f < 1e-6f)) { q[0] = 0.0f; q[1] = 0.0f; q[2] = 0.0f; q[3] = 1.0f; return 0.0f; }
+  q[0] = a; q[1] = b; q[2] = c; q[3] = d;
+  return n;
+}
+
 SB_HD void project_fwd_one(const float* m, const float* s, float glob, const float* q,
                            const Cam& cam, int img_w, int img_h, int bw, float clip, ProjFwd& o) {
   o.valid = false; o.front = false; o.radius = 0; o.tiles = 0;

@@ -44,7 +44,7 @@ def _raw_inputs(gs_params: Dict[str, Tensor]):
     and the degree-0 sigmoid colour (:65) are applied inside the projection kernels, and the backward
     returns gradients w.r.t. these raw tensors directly."""
     gp = {k: (v.float() if v.dtype == torch.half else v) for k, v in gs_params.items()}
-    flags = _abi.FLAG_RAW_SCALES | _abi.FLAG_C2W_OPENGL
+    flags = _abi.FLAG_RAW_SCALES | _abi.FLAG_RAW_QUATS | _abi.FLAG_C2W_OPENGL
     if "opacities" in gp:
         opacities, flags = gp["opacities"], flags | _abi.FLAG_RAW_OPACITIES
     elif "opacities_sigmoid" in gp:
@@ -80,7 +80,7 @@ def _intrinsics(fx, fy, cx, cy, v: int, device) -> Tensor:
 
 
 def render_scene(gs_params: Dict[str, Tensor], camera_to_worlds: Tensor, cx, cy, fx, fy, width, height,
-                 background_color: Tensor, **kwargs) -> Tuple[Tensor, Tensor]:
+                 background_color: Tensor, plan=None, **kwargs) -> Tuple[Tensor, Tensor]:
     """All views at once: rgb (V,H,W,3) clamped to <= 1 and alpha (V,H,W,1)."""
     means, scales, quats, opacities, dc, rest, sh_degree, flags = _raw_inputs(gs_params)
     c2w = camera_to_worlds.to(means.device)
@@ -92,12 +92,12 @@ def render_scene(gs_params: Dict[str, Tensor], camera_to_worlds: Tensor, cx, cy,
     intrins = _intrinsics(fx, fy, cx, cy, v, means.device)
     rgb, alpha = render_views(means, scales, quats, opacities, dc, sh_degree, c2w, None, intrins, h, w,
                               BLOCK_WIDTH, background=background_color.to(means.device), clamp_rgb=True,
-                              color_rest=rest, flags=flags | _abi.FLAG_INTRINS_SHARED)
+                              color_rest=rest, flags=flags | _abi.FLAG_INTRINS_SHARED, plan=plan)
     return rgb, alpha.unsqueeze(-1)
 
 
 def render_l1_loss(gs_params: Dict[str, Tensor], cameras: Dict[str, Tensor], images: Tensor,
-                   return_images: bool = False):
+                   return_images: bool = False, plan=None):
     """The render loss of SplatFormer's training step in one call (train.py:272-278):
 
         pred_imgs, _ = rasterize_gaussians_to_multiimgs(out_gs, cameras)
@@ -106,9 +106,12 @@ def render_l1_loss(gs_params: Dict[str, Tensor], cameras: Dict[str, Tensor], ima
     images: (V,H,W,3) float32 targets in [0,1] on the device.  Returns (l1 (V,), mse (V,)) -- the
     per-view means of |pred - gt| (differentiable w.r.t. the raw Gaussian parameters) and of
     (pred - gt)^2 (for PSNR = -10 log10 mse; not differentiable) -- and the predicted images
-    (V,H,W,3) if return_images.  The image size comes from `images`, so no host synchronisation is
-    spent on cameras['height'/'width']; the loss and its gradient image are computed inside the
-    raster kernels and never exist as tensors."""
+    (V,H,W,3) if return_images; those are differentiable as well, so an image-space term (the
+    reference's LPIPS loss, train.py:276-277) can be added on top of the fused L1: its gradient image
+    enters the raster backward next to sign(pred - gt).  The image size comes from `images`, so no host
+    synchronisation is spent on cameras['height'/'width']; the L1 loss and its gradient image are
+    computed inside the raster kernels and never exist as tensors.  `plan`: render.RenderPlan of the
+    call site (binning capacities learnt from earlier scenes); the module default if omitted."""
     means, scales, quats, opacities, dc, rest, sh_degree, flags = _raw_inputs(gs_params)
     if images.dim() != 4 or images.shape[-1] != 3:
         raise ValueError("images must be (V, H, W, 3)")
@@ -119,7 +122,8 @@ def render_l1_loss(gs_params: Dict[str, Tensor], cameras: Dict[str, Tensor], ima
     intrins = _intrinsics(cameras["fx"], cameras["fy"], cameras["cx"], cameras["cy"], v, means.device)
     l1_sum, sq_sum, rgb = render_views(means, scales, quats, opacities, dc, sh_degree, c2w, None, intrins, h, w,
                                        BLOCK_WIDTH, background=cameras["background_color"].to(means.device),
-                                       clamp_rgb=True, color_rest=rest, flags=flags | _abi.FLAG_INTRINS_SHARED, gt=images)
+                                       clamp_rgb=True, color_rest=rest, flags=flags | _abi.FLAG_INTRINS_SHARED, gt=images,
+                                       plan=plan)
     inv = 1.0 / (h * w * 3)
     out = (l1_sum * inv, sq_sum * inv)
     return out + (rgb,) if return_images else out

@@ -5,9 +5,17 @@ This is the B200-native form of the loop SplatFormer runs in
 (SH, project, cumsum + .item(), emit, sort, bins, rasterise) -- about ten launches and nine host
 synchronisations per view -- every stage is launched once for the whole (V, N) / (V, H, W) batch
 through the C ABI, view-independent data (SH coefficients, Gaussian parameters) is read from HBM
-once per scene, and the per-Gaussian gradients are summed over the views in registers.
+once per scene, and the per-Gaussian gradients are summed over the views on chip.
 Results are the ones the per-view gsplat-compatible API (`splatformer_b200.api`) produces: the
 same device functions run underneath.
+
+Host synchronisation.  A training step (some input requires grad) is enqueued WITHOUT any host
+synchronisation: the tile-segment binning reports "a tile overflowed its segment" through a flag the
+device writes into pinned host memory, and that flag is only looked at when the backward starts (by
+then the device is long past the point that produced it; the forward rasteriser is still running, so
+the GPU never waits for the host).  On the rare overflow the forward is replayed right there with the
+global sort, overwriting the image / loss buffers in place, and the backward continues on the
+corrected state.  Without autograd (evaluation) the flag is read right after the forward.
 """
 from __future__ import annotations
 
@@ -54,12 +62,6 @@ class StageTimer:
 
 
 _timer: Optional[StageTimer] = None
-_last_num_intersects = 0
-
-
-def last_num_intersects() -> int:
-    """Intersections (over all views) of the most recent render_views call (bench.py reports it)."""
-    return _last_num_intersects
 
 
 @contextlib.contextmanager
@@ -88,9 +90,6 @@ def _c(t: Tensor) -> Tensor:
     return _abi.aligned16(t.contiguous())
 
 
-_side_streams: Dict[int, torch.cuda.Stream] = {}
-_pinned: Dict[int, Tensor] = {}
-_overflowed: Dict[Tuple[int, int, int], int] = {}
 USE_RECT_LISTS = True               # fused path, block width 16: rect-list rasteriser (csrc/raster_rect.cu)
 DEFAULT_TILE_CAPACITY = 2048        # doubled per overflow of a (views, tiles, Gaussians) shape, up to the library's limit
 # Scenes whose Gaussians cover many tiles each (large screen radii: a room seen from inside, the 4K stress
@@ -98,30 +97,93 @@ DEFAULT_TILE_CAPACITY = 2048        # doubled per overflow of a (views, tiles, G
 # millions of contended atomics and scattered 8-byte stores.  A shape that averaged more tiles per
 # (view, Gaussian) than this goes to the global sort from its next call on.
 GLOBAL_SORT_TILES_PER_GAUSSIAN = 16.0
-_prefer_global: Dict[Tuple[int, int, int], bool] = {}
 
 
-def _pinned_pair(device) -> Tensor:
-    idx = device.index if device.index is not None else torch.cuda.current_device()
-    if idx not in _pinned:
-        _pinned[idx] = torch.zeros(2, dtype=I32).pin_memory()
-    return _pinned[idx]
+class _Totals:
+    """The two ints the tile sort reports -- [0] intersections, [1] overflow flag -- on their way to the
+    host: a pinned buffer, the event after which it is valid, and the plan entry they belong to."""
+
+    __slots__ = ("host", "event", "key", "plan", "value", "folded")
+
+    def __init__(self, host: Optional[Tensor], event, key, plan, value: Optional[Tuple[int, int]] = None):
+        self.host, self.event, self.key, self.plan, self.value, self.folded = host, event, key, plan, value, False
+
+    def ready(self) -> bool:
+        return self.value is not None or self.event.query()
+
+    def read(self) -> Tuple[int, int]:
+        """(intersections, overflow); waits for the device to have produced them."""
+        if self.value is None:
+            self.event.synchronize()
+            self.value = (int(self.host[0]), int(self.host[1]))
+        if not self.folded:
+            self.folded = True
+            self.plan._fold(self.key, *self.value)
+        return self.value
 
 
-def _tile_capacity(lib, v: int, num_tiles: int, n: int) -> int:
-    """Segment capacity for the tile sort, or 0 to use the global sort.  A (views, tiles, Gaussians)
-    shape whose tiles overflowed the capacity gets twice the capacity next time; past the library's
-    limit it goes straight to the global sort."""
-    if _prefer_global.get((v, num_tiles, n)):
-        return 0
-    cap = DEFAULT_TILE_CAPACITY << _overflowed.get((v, num_tiles, n), 0)
-    if cap > lib.sb_tile_sort_capacity() or v * num_tiles * cap >= 2 ** 31:
-        return 0
-    return cap
+class RenderPlan:
+    """What a call site has learnt about its scenes' binning: the tile-segment capacity per
+    (views, tiles, Gaussians) shape (doubled after an overflow) and whether the shape is better served by
+    the global sort.  `render_views(..., plan=...)` lets every caller keep its own; the module-level
+    default is only used when none is passed."""
+
+    def __init__(self, tile_capacity: Optional[int] = None):
+        self.tile_capacity = tile_capacity
+        self.overflowed: Dict[Tuple[int, int, int], int] = {}
+        self.prefer_global: Dict[Tuple[int, int, int], bool] = {}
+        self.pending: List[_Totals] = []
+        self.last: Optional[_Totals] = None
+        self.replays = 0
+
+    def capacity(self, lib, v: int, num_tiles: int, n: int) -> int:
+        """Segment capacity for the tile sort, or 0 to use the global sort."""
+        self.poll()
+        key = (v, num_tiles, n)
+        if self.prefer_global.get(key):
+            return 0
+        base = self.tile_capacity if self.tile_capacity is not None else DEFAULT_TILE_CAPACITY
+        cap = base << self.overflowed.get(key, 0)
+        if cap > lib.sb_tile_sort_capacity() or v * num_tiles * cap >= 2 ** 31:
+            return 0
+        return cap
+
+    def poll(self) -> None:
+        """Fold in the totals of earlier calls that have reached the host by now (never blocks)."""
+        keep = []
+        for t in self.pending:
+            if t.ready():
+                t.read()
+            else:
+                keep.append(t)
+        self.pending = keep
+
+    def _fold(self, key, num_intersects: int, overflow: int) -> None:
+        if overflow:
+            self.overflowed[key] = self.overflowed.get(key, 0) + 1
+        v, _, n = key
+        if num_intersects > GLOBAL_SORT_TILES_PER_GAUSSIAN * v * n:
+            self.prefer_global[key] = True
+
+    def last_num_intersects(self) -> int:
+        return self.last.read()[0] if self.last is not None else 0
 
 
-def _note_overflow(v: int, num_tiles: int, n: int) -> None:
-    _overflowed[(v, num_tiles, n)] = _overflowed.get((v, num_tiles, n), 0) + 1
+_default_plan = RenderPlan()
+_last_plan: RenderPlan = _default_plan
+# Tests that inspect the binning of a pass made under torch.no_grad() (no grad_fn to reach it through) set
+# KEEP_LAST_PASS; the pass object (device buffers of the whole step) then stays alive until the next call.
+KEEP_LAST_PASS = False
+_last_pass = None
+
+
+def last_num_intersects() -> int:
+    """Intersections (over all views) of the most recent render_views call (waits for that call's
+    binning to finish on the device; bench.py and the tests read it outside the timed loops)."""
+    return _last_plan.last_num_intersects()
+
+
+_side_streams: Dict[int, torch.cuda.Stream] = {}
 
 
 def _side_stream(device) -> torch.cuda.Stream:
@@ -131,274 +193,396 @@ def _side_stream(device) -> torch.cuda.Stream:
     return _side_streams[idx]
 
 
+class _Pass:
+    """The device work of one forward pass.  Kept as an object so that the backward can replay it (global
+    sort) over the same output buffers when the optimistic tile-segment binning turns out to have overflowed."""
+
+    def __init__(self, lib, st, inputs, meta, gt, gt_ready):
+        self.lib, self.st = lib, st
+        (self.means, self.scales, self.quats, self.opacities, self.color_src, self.color_rest, self.viewmats,
+         self.campos, self.intrins, self.background) = inputs
+        (self.v, self.n, self.sh_degree, self.flags, self.h, self.w, self.bw, self.clip, self.vm_stride,
+         self.clamp_rgb) = meta
+        self.gt, self.gt_ready = gt, gt_ready
+        self.gt_dtype = None if gt is None else gt.dtype
+        self.tiles_x = (self.w + self.bw - 1) // self.bw
+        self.tiles_y = (self.h + self.bw - 1) // self.bw
+        self.num_tiles = self.tiles_x * self.tiles_y
+        dev = self.means.device
+        v, n = self.v, self.n
+        self.packed = torch.empty(v, n, 12, dtype=F32, device=dev)
+        self.depths = torch.empty(v, n, dtype=F32, device=dev)
+        self.radii = torch.empty(v, n, dtype=I32, device=dev)
+        self.tiles_hit = torch.empty(v, n, dtype=I32, device=dev)
+        self.out_img = self.final_ts = self.final_idx = self.out_alpha = None
+        self.loss_sums = None           # (V, 2) per-view sums of |rgb - gt| and (rgb - gt)^2, updated in place on a replay
+        self.gids_sorted = self.tile_bins = self.rect_ids = self.rect_counts = None
+        self.cap = 0
+
+    # ---- buffers -------------------------------------------------------------------------------
+    def alloc_images(self):
+        # after the projection kernel is on its way: the host reaches the first launch sooner
+        if self.out_img is not None:
+            return
+        dev, v, h, w = self.means.device, self.v, self.h, self.w
+        self.out_img = torch.empty(v, h, w, 3, dtype=F32, device=dev)
+        self.final_ts = torch.empty(v, h, w, dtype=F32, device=dev)
+        self.final_idx = torch.empty(v, h, w, dtype=I32, device=dev)
+        self.out_alpha = None if self.gt is not None else torch.empty(v, h, w, dtype=F32, device=dev)
+
+    def _loss_partial(self, per_tile: int):
+        if self.gt is None:
+            return None
+        return torch.empty(self.v, self.num_tiles * per_tile, 2, dtype=F32, device=self.means.device)
+
+    def _finish_loss(self, partial):
+        if partial is None:
+            return
+        sums = partial.sum(dim=1)                           # (V, 2)
+        if self.loss_sums is None:
+            self.loss_sums = sums
+        else:
+            self.loss_sums.data.copy_(sums)                 # replay: late readers see the corrected values
+
+    # ---- stages --------------------------------------------------------------------------------
+    def project(self, tile_counts, tile_keys, cap):
+        lib, p = self.lib, _abi.ptr
+        with _stage("project_sh_fwd"):
+            _abi.check(lib.sb_views_project_fwd(
+                self.v, self.n, p(self.means, F32, "means"), p(self.scales, F32, "scales"), 1.0,
+                p(self.quats, F32, "quats"), p(self.opacities, F32, "opacities"),
+                p(self.color_src, F32, "color_src"), p(self.color_rest, F32, "color_rest"), self.sh_degree,
+                self.flags, p(self.viewmats, F32, "viewmats"), self.vm_stride, p(self.intrins, F32, "intrins"), 0.0,
+                0.0, 0.0, 0.0, p(self.campos, F32, "campos"), self.h, self.w, self.bw,
+                self.clip, p(self.packed, F32, "packed"), p(self.depths, F32, "depths"),
+                p(self.radii, I32, "radii"), p(self.tiles_hit, I32, "num_tiles_hit"),
+                p(tile_counts, I32, "tile_counts"), p(tile_keys, torch.int64, "tile_keys"), cap,
+                self.st), "sb_views_project_fwd")
+
+    def _wait_gt(self):
+        if self.gt_ready is not None:
+            torch.cuda.current_stream().wait_event(self.gt_ready)
+
+    def raster_rect(self, view_has, work):
+        lib, p = self.lib, _abi.ptr
+        self._wait_gt()
+        partial = self._loss_partial(8)
+        with _stage("raster_fwd"):
+            _abi.check(lib.sb_rasterize_rect_fwd(
+                self.v, self.n, p(self.packed, F32, "packed"), p(self.rect_ids, I32, "rect_ids"),
+                p(self.rect_counts, I32, "rect_counts"), self.cap, p(self.background, F32, "background"),
+                self.h, self.w, p(view_has, I32, "view_has_isects"),
+                p(self.out_img, F32, "out_img"), p(self.final_ts, F32, "final_Ts"),
+                p(self.final_idx, I32, "final_idx"), p(self.out_alpha, F32, "out_alpha"),
+                1 if self.clamp_rgb else 0, p(self.gt, self.gt_dtype, "gt"), 1 if self.gt_dtype == torch.uint8 else 0,
+                p(partial, F32, "loss_partial"), p(work, I32, "work_counter"), self.st),
+                "sb_rasterize_rect_fwd")
+        self._finish_loss(partial)
+
+    def raster_tiles(self, view_has):
+        lib, p = self.lib, _abi.ptr
+        self._wait_gt()
+        partial = self._loss_partial(1)
+        with _stage("raster_fwd"):
+            _abi.check(lib.sb_rasterize_fwd(
+                self.v, self.n, p(self.packed, F32, "packed"), p(self.gids_sorted, I32, "gaussian_ids_sorted"),
+                p(self.tile_bins, I32, "tile_bins"), p(self.background, F32, "background"), self.h,
+                self.w, self.bw, p(view_has, I32, "view_has_isects"),
+                p(self.out_img, F32, "out_img"), p(self.final_ts, F32, "final_Ts"),
+                p(self.final_idx, I32, "final_idx"), p(self.out_alpha, F32, "out_alpha"),
+                1 if self.clamp_rgb else 0, p(self.gt, self.gt_dtype, "gt"), 1 if self.gt_dtype == torch.uint8 else 0,
+                p(partial, F32, "loss_partial"), self.st), "sb_rasterize_fwd")
+        self._finish_loss(partial)
+
+    # ---- the two binning strategies --------------------------------------------------------------
+    def run_segments(self, cap: int, plan: RenderPlan) -> _Totals:
+        """Fixed-capacity tile segments + per-tile sort (csrc/tile_sort.cu) + rect-list rasteriser, all
+        enqueued without waiting for anything; returns the totals on their way to the host."""
+        lib, p = self.lib, _abi.ptr
+        dev, v, num_tiles = self.means.device, self.v, self.num_tiles
+        self.cap = cap
+        with _stage("zero_counts"):
+            state = torch.zeros(v * num_tiles + v + 4, dtype=I32, device=dev)
+        tile_counts, view_has, totals = state[:v * num_tiles], state[v * num_tiles:-4], state[-4:-2]
+        work = state[-2:]               # rectangle queue heads of the persistent raster kernels
+        tile_keys = torch.empty(v * num_tiles * cap, dtype=torch.int64, device=dev)
+        self.project(tile_counts, tile_keys, cap)
+        self.alloc_images()
+        self.gids_sorted = torch.empty(v * num_tiles * cap, dtype=I32, device=dev)
+        self.tile_bins = torch.empty(v * num_tiles, 2, dtype=I32, device=dev)
+        use_rect = self.bw == 16 and USE_RECT_LISTS
+        if use_rect:
+            # per-rectangle lists for the rect-list rasteriser (one warp per 8x4 rectangle)
+            self.rect_ids = torch.empty(v * num_tiles * 8 * cap, dtype=I32, device=dev)
+            self.rect_counts = torch.empty(v * num_tiles * 8, dtype=I32, device=dev)
+        with _stage("sort_tiles"):
+            _abi.check(lib.sb_sort_tiles(
+                v, num_tiles, cap, p(tile_counts, I32, "tile_counts"),
+                p(tile_keys, torch.int64, "tile_keys"), p(self.gids_sorted, I32, "gaussian_ids_sorted"),
+                p(self.tile_bins, I32, "tile_bins"), p(view_has, I32, "view_has_isects"),
+                p(totals, I32, "totals"), self.n, self.tiles_x, p(self.packed, F32, "packed"),
+                p(self.rect_ids, I32, "rect_ids"), p(self.rect_counts, I32, "rect_counts"),
+                self.st), "sb_sort_tiles")
+        host_totals = torch.empty(2, dtype=I32, pin_memory=True)
+        host_totals.copy_(totals, non_blocking=True)
+        ready = torch.cuda.Event()
+        ready.record()
+        # the raster kernel is enqueued optimistically: the device produced the flag BEFORE it starts
+        if use_rect:
+            self.raster_rect(view_has, work[:1])
+        else:
+            self.raster_tiles(view_has)
+        return _Totals(host_totals, ready, (v, num_tiles, self.n), plan)
+
+    def run_global(self, plan: RenderPlan, projected: bool) -> _Totals:
+        """Very deep tiles / many tiles per Gaussian: depth pre-order of the Gaussians, emission in that
+        order, radix sort over the tile bits only, per-tile rasteriser (one host read of the count)."""
+        if not projected:
+            self.project(None, None, 0)
+        self.alloc_images()
+        self.cap = 0
+        self.rect_ids = self.rect_counts = None
+        with _stage("global_sort"):
+            num_intersects, _, self.gids_sorted, self.tile_bins, view_ends = utils.bin_depth_ordered(
+                self.v, self.n, self.packed, 12, self.depths.view(-1), self.radii.view(-1), self.tiles_hit,
+                (self.tiles_x, self.tiles_y, 1), self.bw, compact=True)
+        view_has = (torch.diff(view_ends, prepend=view_ends.new_zeros(1)) > 0).to(I32)
+        self.raster_tiles(view_has)
+        return _Totals(None, None, (self.v, self.num_tiles, self.n), plan, value=(num_intersects, 0))
+
+
+def grad_layout(n: int, color_shape, rest_shape) -> Tuple[List[Tuple[str, int, Tuple[int, ...]]], int]:
+    """Blocks of the flat per-Gaussian gradient buffer the backward writes, [(name, offset, shape)], and the
+    buffer's size in floats.  One allocation, so that a view-sharded scene can all-reduce it in place
+    (dist.SyncGaussianGrads)."""
+    blocks, off = [], 0
+    for name, shape in (("means", (n, 3)), ("scales", (n, 3)), ("quats", (n, 4)), ("opacities", (n, 1)),
+                        ("color_src", tuple(color_shape)), ("color_rest", None if rest_shape is None else tuple(rest_shape))):
+        if shape is None:
+            continue
+        size = 1
+        for d in shape:
+            size *= d
+        blocks.append((name, off, shape))
+        off += (size + 3) // 4 * 4           # every block starts 16-byte aligned
+    return blocks, off
+
+
 class _RenderViews(Function):
     """One autograd node for the whole scene.
 
     `flags` (see _abi.FLAG_*) tell the kernels which of the wrapper's activations they apply
     themselves; `color_rest` is features_rest when the SH coefficients arrive split as SplatFormer
-    stores them.  With `gt` given the node returns the per-view L1 and squared-error sums instead of
-    leaving the loss to torch (train.py:275,278) and the backward derives the image gradient inside
-    the raster kernel."""
+    stores them.  With `gt` given the node returns the per-view L1 and squared-error sums next to the
+    images (train.py:275,278) and the backward derives the L1 part of the image gradient inside the
+    raster kernel; a gradient arriving on the returned images (LPIPS / SSIM terms, train.py:276-277)
+    is added to it."""
 
     @staticmethod
     def forward(ctx, means, scales, quats, opacities, color_src, color_rest, viewmats, campos, intrins, gt,
-                sh_degree, flags, img_height, img_width, block_width, background, clip_thresh, clamp_rgb):
-        lib = _abi.load()
-        st = _abi.stream()                      # one current-stream lookup per pass (it costs ~20 us)
+                sh_degree, flags, img_height, img_width, block_width, background, clip_thresh, clamp_rgb, plan):
+        global _last_plan
         dev = means.device
-        n = means.shape[0]
-        v = viewmats.shape[0]
-        means, scales, quats = _c(means), _c(scales), _c(quats)
-        opacities = _c(opacities).view(-1)
-        color_src = _c(color_src)
-        color_rest = None if color_rest is None else _c(color_rest)
-        viewmats = _c(viewmats.to(F32))
-        vm_stride = viewmats.shape[1] * viewmats.shape[2]
-        campos = None if campos is None else _c(campos.to(F32))
-        intrins = _c(intrins.to(F32))
-        background = _c(background.to(F32))
-        gt_ready = None
-        if gt is not None:
-            if gt.dtype not in (torch.uint8, F32):
-                gt = gt.to(F32)
-            if not gt.is_cuda:
-                # targets in (pinned) host memory: the upload runs on a side stream underneath the
-                # projection / sort stages and is awaited right before the raster kernel needs it
-                side = _side_stream(dev)
-                with torch.cuda.stream(side):
-                    gt = gt.contiguous().to(dev, non_blocking=True)
-                    gt_ready = torch.cuda.Event()
-                    gt_ready.record(side)
-                gt.record_stream(torch.cuda.current_stream())
-            gt = _c(gt)
-        gt_dtype = None if gt is None else gt.dtype
-        tiles_x = (img_width + block_width - 1) // block_width
-        tiles_y = (img_height + block_width - 1) // block_width
-
-        packed = torch.empty(v, n, 12, dtype=F32, device=dev)
-        depths = torch.empty(v, n, dtype=F32, device=dev)
-        radii = torch.empty(v, n, dtype=I32, device=dev)
-        tiles_hit = torch.empty(v, n, dtype=I32, device=dev)
-        num_tiles = tiles_x * tiles_y
-        out_img = final_ts = final_idx = out_alpha = None
-
-        def alloc_images():
-            # after the projection kernel is on its way: the host reaches the first launch sooner
-            nonlocal out_img, final_ts, final_idx, out_alpha
-            out_img = torch.empty(v, img_height, img_width, 3, dtype=F32, device=dev)
-            final_ts = torch.empty(v, img_height, img_width, dtype=F32, device=dev)
-            final_idx = torch.empty(v, img_height, img_width, dtype=I32, device=dev)
-            out_alpha = None if gt is not None else torch.empty(v, img_height, img_width, dtype=F32, device=dev)
-        # per-tile loss sums (fallback raster kernel) or per-rectangle sums (rect-list kernel)
-        loss_buf = [None]
-
-        def loss_partials(per_tile):
-            loss_buf[0] = None if gt is None else torch.empty(v, num_tiles * per_tile, 2, dtype=F32, device=dev)
-            return loss_buf[0]
-
-        def project(tile_counts, tile_keys, cap):
-            with _stage("project_sh_fwd"):
-                _abi.check(lib.sb_views_project_fwd(
-                    v, n, _abi.ptr(means, F32, "means"), _abi.ptr(scales, F32, "scales"), 1.0,
-                    _abi.ptr(quats, F32, "quats"), _abi.ptr(opacities, F32, "opacities"),
-                    _abi.ptr(color_src, F32, "color_src"), _abi.ptr(color_rest, F32, "color_rest"), sh_degree,
-                    flags, _abi.ptr(viewmats, F32, "viewmats"), vm_stride, _abi.ptr(intrins, F32, "intrins"), 0.0,
-                    0.0, 0.0, 0.0, _abi.ptr(campos, F32, "campos"), img_height, img_width, block_width,
-                    clip_thresh, _abi.ptr(packed, F32, "packed"), _abi.ptr(depths, F32, "depths"),
-                    _abi.ptr(radii, I32, "radii"), _abi.ptr(tiles_hit, I32, "num_tiles_hit"),
-                    _abi.ptr(tile_counts, I32, "tile_counts"), _abi.ptr(tile_keys, torch.int64, "tile_keys"), cap,
-                    st), "sb_views_project_fwd")
-
-        def raster_rect(rect_ids, rect_counts, cap, view_has, work):
-            if gt_ready is not None:
-                torch.cuda.current_stream().wait_event(gt_ready)
-            loss_partial = loss_partials(8)
-            with _stage("raster_fwd"):
-                _abi.check(lib.sb_rasterize_rect_fwd(
-                    v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(rect_ids, I32, "rect_ids"),
-                    _abi.ptr(rect_counts, I32, "rect_counts"), cap, _abi.ptr(background, F32, "background"),
-                    img_height, img_width, _abi.ptr(view_has, I32, "view_has_isects"),
-                    _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
-                    _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
-                    1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,
-                    _abi.ptr(loss_partial, F32, "loss_partial"), _abi.ptr(work, I32, "work_counter"), st),
-                    "sb_rasterize_rect_fwd")
-
-        def raster(gids_sorted, tile_bins, view_has):
-            if gt_ready is not None:
-                torch.cuda.current_stream().wait_event(gt_ready)
-            loss_partial = loss_partials(1)
-            with _stage("raster_fwd"):
-                _abi.check(lib.sb_rasterize_fwd(
-                    v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
-                    _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
-                    img_width, block_width, _abi.ptr(view_has, I32, "view_has_isects"),
-                    _abi.ptr(out_img, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
-                    _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"),
-                    1 if clamp_rgb else 0, _abi.ptr(gt, gt_dtype, "gt"), 1 if gt_dtype == torch.uint8 else 0,
-                    _abi.ptr(loss_partial, F32, "loss_partial"), st), "sb_rasterize_fwd")
-
-        global _last_num_intersects
-        cap = _tile_capacity(lib, v, num_tiles, n)
-        done = False
-        rect_ids = rect_counts = None
-        if cap:
-            # fixed-capacity tile segments + per-tile sort (csrc/tile_sort.cu).  The raster kernel is
-            # enqueued optimistically; the host then reads the overflow flag, which the GPU produced
-            # BEFORE the raster kernel started -- the device never idles on this round trip.
-            with _stage("zero_counts"):
-                state = torch.zeros(v * num_tiles + v + 4, dtype=I32, device=dev)
-            tile_counts, view_has, totals = state[:v * num_tiles], state[v * num_tiles:-4], state[-4:-2]
-            work = state[-2:]               # rectangle queue heads of the persistent raster kernels
-            tile_keys = torch.empty(v * num_tiles * cap, dtype=torch.int64, device=dev)
-            project(tile_counts, tile_keys, cap)
-            alloc_images()
-            gids_sorted = torch.empty(v * num_tiles * cap, dtype=I32, device=dev)
-            tile_bins = torch.empty(v * num_tiles, 2, dtype=I32, device=dev)
-            use_rect = block_width == 16 and USE_RECT_LISTS
-            if use_rect:
-                # per-rectangle lists for the rect-list rasteriser (one warp per 8x4 rectangle)
-                rect_ids = torch.empty(v * num_tiles * 8 * cap, dtype=I32, device=dev)
-                rect_counts = torch.empty(v * num_tiles * 8, dtype=I32, device=dev)
-            with _stage("sort_tiles"):
-                _abi.check(lib.sb_sort_tiles(
-                    v, num_tiles, cap, _abi.ptr(tile_counts, I32, "tile_counts"),
-                    _abi.ptr(tile_keys, torch.int64, "tile_keys"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
-                    _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(view_has, I32, "view_has_isects"),
-                    _abi.ptr(totals, I32, "totals"), n, tiles_x, _abi.ptr(packed, F32, "packed"),
-                    _abi.ptr(rect_ids, I32, "rect_ids"), _abi.ptr(rect_counts, I32, "rect_counts"),
-                    st), "sb_sort_tiles")
-            host_totals = _pinned_pair(dev)
-            host_totals.copy_(totals, non_blocking=True)
-            flag_ready = torch.cuda.Event()
-            flag_ready.record()
-            if use_rect:
-                raster_rect(rect_ids, rect_counts, cap, view_has, work[:1])
+        with torch.cuda.device(dev):
+            lib = _abi.load()
+            st = _abi.stream()                      # one current-stream lookup per pass (it costs ~20 us)
+            n = means.shape[0]
+            v = viewmats.shape[0]
+            opac_shape = tuple(opacities.shape)
+            means, scales, quats = _c(means), _c(scales), _c(quats)
+            opacities = _c(opacities).view(-1)
+            color_src = _c(color_src)
+            color_rest = None if color_rest is None else _c(color_rest)
+            viewmats = _c(viewmats.to(F32))
+            vm_stride = viewmats.shape[1] * viewmats.shape[2]
+            campos = None if campos is None else _c(campos.to(F32))
+            intrins = _c(intrins.to(F32))
+            background = _c(background.to(F32))
+            gt_ready = None
+            if gt is not None:
+                if gt.dtype not in (torch.uint8, F32):
+                    gt = gt.to(F32)
+                if not gt.is_cuda:
+                    # targets in (pinned) host memory: the upload runs on a side stream underneath the
+                    # projection / sort stages and is awaited right before the raster kernel needs it
+                    side = _side_stream(dev)
+                    with torch.cuda.stream(side):
+                        gt = gt.contiguous().to(dev, non_blocking=True)
+                        gt_ready = torch.cuda.Event()
+                        gt_ready.record(side)
+                    gt.record_stream(torch.cuda.current_stream())
+                gt = _c(gt)
+            meta = (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride, clamp_rgb)
+            ps = _Pass(lib, st, (means, scales, quats, opacities, color_src, color_rest, viewmats, campos, intrins,
+                                 background), meta, gt, gt_ready)
+            training = any(ctx.needs_input_grad[:6])       # False under torch.no_grad() / for constant inputs
+            cap = plan.capacity(lib, v, ps.num_tiles, n)
+            if cap:
+                totals = ps.run_segments(cap, plan)
+                if not training:
+                    # evaluation: nothing will come back to repair an overflowed pass, look right away
+                    if totals.read()[1]:
+                        plan.replays += 1
+                        totals = ps.run_global(plan, projected=True)
+                else:
+                    plan.pending.append(totals)
             else:
-                raster(gids_sorted, tile_bins, view_has)
-            flag_ready.synchronize()
-            num_intersects, overflow = int(host_totals[0]), int(host_totals[1])
-            done = overflow == 0
-            if num_intersects > GLOBAL_SORT_TILES_PER_GAUSSIAN * v * n:
-                _prefer_global[(v, num_tiles, n)] = True
-            if not done:
-                _note_overflow(v, num_tiles, n)
-                rect_ids = rect_counts = None
-        if not done:
-            # very deep tiles / many tiles per Gaussian: global sort over all (tile, Gaussian) pairs
-            if not cap:
-                project(None, None, 0)
-                alloc_images()
-            # depth pre-order of the Gaussians, emission in that order, radix sort over the tile bits only
-            with _stage("global_sort"):
-                num_intersects, _, gids_sorted, tile_bins, view_ends = utils.bin_depth_ordered(
-                    v, n, packed, 12, depths.view(-1), radii.view(-1), tiles_hit, (tiles_x, tiles_y, 1), block_width,
-                    compact=True)
-            view_has = (torch.diff(view_ends, prepend=view_ends.new_zeros(1)) > 0).to(I32)
-            raster(gids_sorted, tile_bins, view_has)
-        _last_num_intersects = num_intersects
-        ctx.meta = (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride,
-                    tuple(color_src.shape), None if color_rest is None else tuple(color_rest.shape),
-                    num_intersects, clamp_rgb, cap)
-        keep_img = clamp_rgb or gt is not None
-        ctx.save_for_backward(means, scales, quats, viewmats, campos, intrins, background, packed,
-                              gids_sorted, tile_bins, final_ts, final_idx, out_img if keep_img else None, gt,
-                              rect_ids, rect_counts)
-        ctx.set_materialize_grads(False)
-        if gt is not None:
-            sums = loss_buf[0].sum(dim=1)                       # (V, 2): sum |rgb - gt|, sum (rgb - gt)^2
-            l1_sum, sq_sum = sums[:, 0], sums[:, 1]
-            ctx.mark_non_differentiable(sq_sum, out_img)
-            return l1_sum, sq_sum, out_img
-        return out_img, out_alpha
+                totals = ps.run_global(plan, projected=False)
+                totals.read()
+            plan.last = totals
+            _last_plan = plan
+            if KEEP_LAST_PASS:
+                global _last_pass
+                _last_pass = ps
+            ctx.ps, ctx.totals, ctx.plan = ps, totals, plan
+            ctx.opac_shape = opac_shape
+            ctx.color_shapes = (tuple(color_src.shape), None if color_rest is None else tuple(color_rest.shape))
+            ctx.set_materialize_grads(False)
+            if gt is not None:
+                l1_sum, sq_sum = ps.loss_sums[:, 0], ps.loss_sums[:, 1]
+                ctx.mark_non_differentiable(sq_sum)
+                return l1_sum, sq_sum, ps.out_img
+            return ps.out_img, ps.out_alpha
 
     @staticmethod
     def backward(ctx, *grads):
-        lib = _abi.load()
-        st = _abi.stream()
-        (means, scales, quats, viewmats, campos, intrins, background, packed, gids_sorted, tile_bins,
-         final_ts, final_idx, out_img, gt, rect_ids, rect_counts) = ctx.saved_tensors
-        (v, n, sh_degree, flags, img_height, img_width, block_width, clip_thresh, vm_stride, color_shape,
-         rest_shape, num_intersects, clamp_rgb, cap) = ctx.meta
-        dev = means.device
-        nin = 18
-        if gt is not None:
-            v_l1 = grads[0]
-            if v_l1 is None:
+        ps: _Pass = ctx.ps
+        nin = 19
+        dev = ps.means.device
+        if ps.gt is not None:
+            v_l1, _, v_out_img = grads
+            v_out_alpha = None
+            if v_l1 is None and v_out_img is None:
                 return (None,) * nin
-            v_loss = _c(v_l1.to(F32))
-            v_out_img = v_out_alpha = None
         else:
             v_out_img, v_out_alpha = grads
+            v_l1 = None
             if v_out_img is None and v_out_alpha is None:
                 return (None,) * nin
-            v_out_img = None if v_out_img is None else _c(v_out_img)
-            v_out_alpha = None if v_out_alpha is None else _c(v_out_alpha)
+        with torch.cuda.device(dev):
+            lib, p = _abi.load(), _abi.ptr
+            st = _abi.stream()
+            ps.st = st
+            # the binning flag of the forward: the device wrote it before the forward rasteriser started
+            num_intersects, overflow = ctx.totals.read()
+            if overflow:
+                # a tile ran over its segment: the lists the forward walked were truncated.  Redo the pass with
+                # the global sort over the same buffers (images and loss sums are corrected in place), then
+                # differentiate that.
+                ctx.plan.replays += 1
+                stale = ctx.totals
+                ctx.totals = ps.run_global(ctx.plan, projected=True)
+                if ctx.plan.last is stale:
+                    ctx.plan.last = ctx.totals
+            v, n = ps.v, ps.n
             v_loss = None
-        with _stage("zero_grads"):
-            v_packed = torch.zeros(v, n, 12, dtype=F32, device=dev)
-        gt_dt = None if gt is None else gt.dtype
-        if rect_ids is not None:
-            with _stage("raster_bwd"):
-                _abi.check(lib.sb_rasterize_rect_bwd(
-                    v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(rect_ids, I32, "rect_ids"),
-                    _abi.ptr(rect_counts, I32, "rect_counts"), cap, _abi.ptr(background, F32, "background"),
-                    img_height, img_width, _abi.ptr(final_ts, F32, "final_Ts"),
-                    _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(v_out_img, F32, "v_out_img"),
-                    _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(out_img, F32, "out_img"),
-                    1 if clamp_rgb else 0, _abi.ptr(gt, gt_dt, "gt"), 1 if gt_dt == torch.uint8 else 0,
-                    _abi.ptr(v_loss, F32, "v_loss"), _abi.ptr(v_packed, F32, "v_packed"), st),
-                    "sb_rasterize_rect_bwd")
-        else:
-          with _stage("raster_bwd"):
-            _abi.check(lib.sb_rasterize_bwd(
-                v, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gids_sorted, I32, "gaussian_ids_sorted"),
-                _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(background, F32, "background"), img_height,
-                img_width, block_width, _abi.ptr(final_ts, F32, "final_Ts"),
-                _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(v_out_img, F32, "v_out_img"),
-                _abi.ptr(v_out_alpha, F32, "v_out_alpha"), _abi.ptr(out_img, F32, "out_img"),
-                1 if clamp_rgb else 0, _abi.ptr(gt, None if gt is None else gt.dtype, "gt"),
-                1 if (gt is not None and gt.dtype == torch.uint8) else 0, _abi.ptr(v_loss, F32, "v_loss"),
-                _abi.ptr(v_packed, F32, "v_packed"), st), "sb_rasterize_bwd")
-        v_means = torch.empty(n, 3, dtype=F32, device=dev)
-        v_scales = torch.empty(n, 3, dtype=F32, device=dev)
-        v_quats = torch.empty(n, 4, dtype=F32, device=dev)
-        v_opac = torch.empty(n, 1, dtype=F32, device=dev)
-        v_color = torch.empty(color_shape, dtype=F32, device=dev)
-        v_rest = None if rest_shape is None else torch.empty(rest_shape, dtype=F32, device=dev)
-        with _stage("project_sh_bwd"):
-            _abi.check(lib.sb_views_project_bwd(
-                v, n, _abi.ptr(means, F32, "means"), _abi.ptr(scales, F32, "scales"), 1.0,
-                _abi.ptr(quats, F32, "quats"), sh_degree, flags, _abi.ptr(viewmats, F32, "viewmats"), vm_stride,
-                _abi.ptr(intrins, F32, "intrins"), 0.0, 0.0, 0.0, 0.0, _abi.ptr(campos, F32, "campos"),
-                img_height, img_width, block_width, clip_thresh, _abi.ptr(packed, F32, "packed"),
-                _abi.ptr(v_packed, F32, "v_packed"), _abi.ptr(v_means, F32, "v_means"),
-                _abi.ptr(v_scales, F32, "v_scales"), _abi.ptr(v_quats, F32, "v_quats"),
-                _abi.ptr(v_opac, F32, "v_opacities"), _abi.ptr(v_color, F32, "v_color_src"),
-                _abi.ptr(v_rest, F32, "v_color_rest"), st), "sb_views_project_bwd")
-        return (v_means, v_scales, v_quats, v_opac, v_color, v_rest) + (None,) * (nin - 6)
+            if ps.gt is not None:
+                v_loss = torch.zeros(v, dtype=F32, device=dev) if v_l1 is None else _c(v_l1.to(F32))
+            v_out_img = None if v_out_img is None else _c(v_out_img.to(F32))
+            v_out_alpha = None if v_out_alpha is None else _c(v_out_alpha.to(F32))
+            with _stage("zero_grads"):
+                v_packed = torch.zeros(v, n, 12, dtype=F32, device=dev)
+            gt_dt = ps.gt_dtype
+            out_img = ps.out_img if (ps.clamp_rgb or ps.gt is not None) else None
+            if ps.rect_ids is not None:
+                with _stage("raster_bwd"):
+                    _abi.check(lib.sb_rasterize_rect_bwd(
+                        v, n, p(ps.packed, F32, "packed"), p(ps.rect_ids, I32, "rect_ids"),
+                        p(ps.rect_counts, I32, "rect_counts"), ps.cap, p(ps.background, F32, "background"),
+                        ps.h, ps.w, p(ps.final_ts, F32, "final_Ts"),
+                        p(ps.final_idx, I32, "final_idx"), p(v_out_img, F32, "v_out_img"),
+                        p(v_out_alpha, F32, "v_out_alpha"), p(out_img, F32, "out_img"),
+                        1 if ps.clamp_rgb else 0, p(ps.gt, gt_dt, "gt"), 1 if gt_dt == torch.uint8 else 0,
+                        p(v_loss, F32, "v_loss"), p(v_packed, F32, "v_packed"), st),
+                        "sb_rasterize_rect_bwd")
+            else:
+                with _stage("raster_bwd"):
+                    _abi.check(lib.sb_rasterize_bwd(
+                        v, n, p(ps.packed, F32, "packed"), p(ps.gids_sorted, I32, "gaussian_ids_sorted"),
+                        p(ps.tile_bins, I32, "tile_bins"), p(ps.background, F32, "background"), ps.h,
+                        ps.w, ps.bw, p(ps.final_ts, F32, "final_Ts"),
+                        p(ps.final_idx, I32, "final_idx"), p(v_out_img, F32, "v_out_img"),
+                        p(v_out_alpha, F32, "v_out_alpha"), p(out_img, F32, "out_img"),
+                        1 if ps.clamp_rgb else 0, p(ps.gt, gt_dt, "gt"), 1 if gt_dt == torch.uint8 else 0,
+                        p(v_loss, F32, "v_loss"), p(v_packed, F32, "v_packed"), st), "sb_rasterize_bwd")
+            # all per-Gaussian gradients in ONE allocation (dist.SyncGaussianGrads all-reduces it in place)
+            color_shape, rest_shape = ctx.color_shapes
+            blocks, size = grad_layout(n, color_shape, rest_shape)
+            flat = torch.empty(size, dtype=F32, device=dev)
+            g = {}
+            for name, off, shape in blocks:
+                cnt = 1
+                for x in shape:
+                    cnt *= x
+                g[name] = flat[off:off + cnt].view(shape)
+            stats = _bwd_stats(dev) if COLLECT_BWD_STATS else None
+            with _stage("project_sh_bwd"):
+                _abi.check(lib.sb_views_project_bwd(
+                    v, n, p(ps.means, F32, "means"), p(ps.scales, F32, "scales"), 1.0,
+                    p(ps.quats, F32, "quats"), ps.sh_degree, ps.flags, p(ps.viewmats, F32, "viewmats"), ps.vm_stride,
+                    p(ps.intrins, F32, "intrins"), 0.0, 0.0, 0.0, 0.0, p(ps.campos, F32, "campos"),
+                    ps.h, ps.w, ps.bw, ps.clip, p(ps.packed, F32, "packed"),
+                    p(v_packed, F32, "v_packed"), p(g["means"], F32, "v_means"),
+                    p(g["scales"], F32, "v_scales"), p(g["quats"], F32, "v_quats"),
+                    p(g["opacities"], F32, "v_opacities"), p(g["color_src"], F32, "v_color_src"),
+                    p(g.get("color_rest"), F32, "v_color_rest"), p(stats, I32, "stats"), st), "sb_views_project_bwd")
+            return (g["means"], g["scales"], g["quats"], g["opacities"].view(ctx.opac_shape), g["color_src"],
+                    g.get("color_rest")) + (None,) * (nin - 6)
+
+
+# Debug counter of the projection backward: (records scanned, records with a non-zero gradient), summed
+# over the calls made while COLLECT_BWD_STATS is on.  Off by default (two extra atomics per warp).
+COLLECT_BWD_STATS = False
+_bwd_stats_buf: Dict[int, Tensor] = {}
+
+
+def _bwd_stats(device) -> Tensor:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _bwd_stats_buf:
+        _bwd_stats_buf[idx] = torch.zeros(2, dtype=I32, device=device)
+    return _bwd_stats_buf[idx]
+
+
+def bwd_stats(device=None, reset: bool = True) -> Tuple[int, int]:
+    """(records scanned, records with a non-zero gradient) since the last reset (COLLECT_BWD_STATS)."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+    buf = _bwd_stats(device)
+    a, b = (int(x) for x in buf.tolist())
+    if reset:
+        buf.zero_()
+    return a, b
+
+
+def _campos_from_viewmats(viewmats: Tensor) -> Tensor:
+    """Camera centres -R^T t of (V,3|4,4) world->camera matrices."""
+    rot, t = viewmats[:, :3, :3].to(F32), viewmats[:, :3, 3].to(F32)
+    return -(rot.transpose(1, 2) * t[:, None, :]).sum(dim=2)
 
 
 def render_views(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor, color_src: Tensor,
                  sh_degree: int, viewmats: Tensor, campos: Optional[Tensor], intrins: Tensor,
                  img_height: int, img_width: int, block_width: int = 16,
                  background: Optional[Tensor] = None, clip_thresh: float = 0.01, clamp_rgb: bool = False,
-                 color_rest: Optional[Tensor] = None, flags: int = 0, gt: Optional[Tensor] = None):
+                 color_rest: Optional[Tensor] = None, flags: int = 0, gt: Optional[Tensor] = None,
+                 plan: Optional[RenderPlan] = None):
     """Render all V views of one scene.
 
     means (N,3), scales (N,3), quats (N,4), opacities (N,1|N); activated values unless `flags`
-    (_abi.FLAG_RAW_SCALES | FLAG_RAW_OPACITIES | FLAG_COLOR_SIGMOID) say the kernels apply
-    exp / sigmoid themselves.  color_src: (N,K,3) SH coefficients with sh_degree in 0..4 (colour =
-    max(SH + 0.5, 0) as gs_utils.py:78-79; or features_dc (N,3) with color_rest = features_rest
-    (N,K-1,3)), or (N,3) rgb with sh_degree = -1.  viewmats (V,3|4,4) world->camera with campos (V,3)
-    camera centres, or OpenGL camera-to-world matrices with FLAG_C2W_OPENGL; intrins (V,4) = fx, fy, cx, cy,
-    or (1,4) shared by all views with FLAG_INTRINS_SHARED.
+    (_abi.FLAG_RAW_SCALES | FLAG_RAW_OPACITIES | FLAG_RAW_QUATS | FLAG_COLOR_SIGMOID) say the kernels
+    apply exp / sigmoid / the wrapper's quaternion normalisation themselves.  color_src: (N,K,3) SH
+    coefficients with sh_degree in 0..4 (colour = max(SH + 0.5, 0) as gs_utils.py:78-79; or features_dc
+    (N,3) with color_rest = features_rest (N,K-1,3)), or (N,3) rgb with sh_degree = -1.  viewmats
+    (V,3|4,4) world->camera (campos (V,3) = camera centres, derived from the matrices when omitted), or
+    OpenGL camera-to-world matrices with FLAG_C2W_OPENGL; intrins (V,4) = fx, fy, cx, cy, or (1,4) shared
+    by all views with FLAG_INTRINS_SHARED.
 
     Returns rgb (V,H,W,3) and alpha (V,H,W); rgb is not clamped unless clamp_rgb=True, which folds the
     wrapper's torch.clamp(rgb, max=1) (gs_utils.py:111) into the kernels.  With gt (V,H,W,3) given it
     returns instead (l1_sum (V,), sq_sum (V,), rgb): the per-view sums of |rgb - gt| (differentiable)
-    and (rgb - gt)^2 (for PSNR, not differentiable) computed inside the raster kernel.
-    Differentiable in means, scales, quats, opacities, color_src and color_rest."""
+    and (rgb - gt)^2 (for PSNR, not differentiable) computed inside the raster kernel, and the images,
+    which are differentiable too (an image-space loss such as LPIPS can be added on top of the fused L1).
+    Differentiable in means, scales, quats, opacities, color_src and color_rest.
+    `plan` keeps what the call site has learnt about its scenes' binning (RenderPlan)."""
     assert 2 <= block_width <= 16, "block_width must be between 2 and 16"
     if not means.is_cuda:
         raise RuntimeError("render_views needs CUDA tensors (there is no CPU path)")
@@ -408,7 +592,9 @@ def render_views(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor
     if tuple(intrins.shape) != want:
         raise ValueError(f"intrins must be {want}, got {tuple(intrins.shape)}")
     if campos is None and not (flags & _abi.FLAG_C2W_OPENGL):
-        campos = torch.zeros(viewmats.shape[0], 3, dtype=F32, device=means.device)
+        # SH view directions need the camera centres; sh_degree = -1 never reads them
+        campos = _campos_from_viewmats(viewmats) if sh_degree >= 0 else \
+            torch.zeros(viewmats.shape[0], 3, dtype=F32, device=means.device)
     return _RenderViews.apply(means, scales, quats, opacities, color_src, color_rest, viewmats, campos, intrins,
                               gt, int(sh_degree), int(flags), int(img_height), int(img_width), int(block_width),
-                              background, float(clip_thresh), bool(clamp_rgb))
+                              background, float(clip_thresh), bool(clamp_rgb), plan if plan is not None else _default_plan)

@@ -78,3 +78,74 @@ def small_scene(n=600, deg=2, seed=7, size=64, views=2, scale_mult=0.6):
     gs = synth.shell_scene(n, deg, seed=seed, scale_mult=scale_mult)
     cams = synth.orbit_cameras(views, size, size, background=(0.1, 0.2, 0.3))
     return gs, cams
+
+
+# ---------------------------------------------------------------------------------------------
+# The reference's wrapper evaluates its activations with torch ON THE GPU (gs_utils.py:45,54,65).
+# These stand-ins let the CPU oracle see exactly those bits (and differentiate through them), so that
+# a parity test of the raw-parameter path compares the kernels with "what gsplat would have been
+# handed", not with the CPU libm's last-bit choices.
+# ---------------------------------------------------------------------------------------------
+class _GpuExp(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y = torch.exp(x.detach().cuda()).cpu() if x.dtype == torch.float32 else torch.exp(x.detach())
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        (y,) = ctx.saved_tensors
+        return g * y
+
+
+class _GpuSigmoid(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y = torch.sigmoid(x.detach().cuda()).cpu() if x.dtype == torch.float32 else torch.sigmoid(x.detach())
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        (y,) = ctx.saved_tensors
+        return g * y * (1.0 - y)
+
+
+def gpu_exp(x):
+    return _GpuExp.apply(x)
+
+
+def gpu_sigmoid(x):
+    return _GpuSigmoid.apply(x)
+
+
+_REPORT = []
+
+
+def report(**fields):
+    """One line of the parity report (printed, and appended to gpurun_out/parity_report.jsonl when that
+    directory exists): what was compared, how many elements, how many were set aside and why."""
+    import json
+    import os
+    line = json.dumps(fields, sort_keys=True)
+    print("[parity] " + line)
+    _REPORT.append(fields)
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "parity_report.jsonl"), "a") as f:
+            f.write(line + "\n")
+
+
+def tile_lists_from_segments(gids_sorted, tile_bins, view, tiles_per_view):
+    """The fused path's per-tile lists of one view, concatenated in tile order (what the oracle's
+    gaussian_ids_sorted is), and the per-tile lengths."""
+    bins = tile_bins[view * tiles_per_view:(view + 1) * tiles_per_view].long().cpu()
+    cnt = bins[:, 1] - bins[:, 0]
+    total = int(cnt.sum())
+    if total == 0:
+        return torch.zeros(0, dtype=torch.int32), cnt
+    tile_of = torch.repeat_interleave(torch.arange(tiles_per_view), cnt)
+    start_out = torch.cumsum(cnt, 0) - cnt
+    pos = torch.arange(total) - start_out[tile_of] + bins[tile_of, 0]
+    return gids_sorted.cpu()[pos], cnt

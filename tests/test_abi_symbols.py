@@ -40,7 +40,7 @@ def test_library_exports_every_declared_symbol(sb_lib):
                                                        f"{len(_abi.SIGNATURES[name][1])}"
     for name in _abi.SIGNATURES:
         assert name in d, f"{name} bound but not declared in include/splat_b200.h"
-    assert sb_lib.sb_abi_version() == 2
+    assert sb_lib.sb_abi_version() == _abi.ABI_VERSION
     assert b"invalid argument" in sb_lib.sb_error_string(-1)
 
 

@@ -175,8 +175,8 @@ def test_fused_tile_sort_is_bit_identical_to_oracle_tiling(cuda, sb_lib, n, size
     rgb, alpha = render.render_views(a["means"].to(cuda), a["scales"].to(cuda), a["quats"].to(cuda),
                                      a["opacities"].to(cuda).requires_grad_(), torch.sigmoid(gs["features_dc"]).to(cuda),
                                      -1, vms.to(cuda), None, intr.to(cuda), k["H"], k["W"], 16)
-    saved = rgb.grad_fn.saved_tensors
-    gids_sorted, tile_bins = saved[8].cpu(), saved[9].cpu()      # segment layout: tile t owns [t*cap, t*cap+count)
+    ps = rgb.grad_fn.ps                                          # the pass's device state (render._Pass)
+    gids_sorted, tile_bins = ps.gids_sorted.cpu(), ps.tile_bins.cpu()   # segment layout: tile t owns [t*cap, t*cap+count)
     tb = ((k["W"] + 15) // 16, (k["H"] + 15) // 16, 1)
     t = tb[0] * tb[1]
     total = 0
@@ -208,15 +208,24 @@ def test_fused_tile_overflow_falls_back_to_global_sort(cuda, sb_lib, monkeypatch
     raw_a = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
     raw_b = {k_: v.to(cuda).requires_grad_() for k_, v in gs.items()}
     l1_a, _, img_a = gs_utils.render_l1_loss(raw_a, cams, gt, return_images=True)
-    monkeypatch.setattr(render, "DEFAULT_TILE_CAPACITY", 64)
-    monkeypatch.setattr(render, "_overflowed", {})
-    l1_b, _, img_b = gs_utils.render_l1_loss(raw_b, cams, gt, return_images=True)
-    assert render._overflowed, "capacity 64 must overflow on this scene"
+    tight = render.RenderPlan(tile_capacity=64)                  # this call site's plan: segments of 64 keys
+    l1_b, _, img_b = gs_utils.render_l1_loss(raw_b, cams, gt, return_images=True, plan=tight)
+    # a training step is enqueued without a host synchronisation: the overflow is noticed when the backward
+    # starts, which replays the forward with the global sort over the SAME image / loss buffers
+    l1_a.sum().backward(); l1_b.sum().backward()
+    assert tight.overflowed and tight.replays == 1, "capacity 64 must overflow on this scene"
+    assert not render._default_plan.overflowed.get((2, 36, 3000)), "another call site's plan must not be touched"
     # the loss sums per rectangle on the rect-list path and per tile on the fallback: same terms, different order
     assert torch.equal(img_a, img_b) and torch.allclose(l1_a, l1_b, rtol=2e-6, atol=0)
-    l1_a.sum().backward(); l1_b.sum().backward()
     for name in gs:
         H.assert_grad_close(raw_a[name].grad, raw_b[name].grad, name)
+    # evaluation (no autograd): the flag is read right after the forward, the caller only ever sees the repaired pass
+    tight2 = render.RenderPlan(tile_capacity=64)
+    with torch.no_grad():
+        l1_c, _, img_c = gs_utils.render_l1_loss(raw_b, cams, gt, return_images=True, plan=tight2)
+    assert tight2.replays == 1 and torch.equal(img_a, img_c)
+    # the plan has learnt: the next call of this site starts with a larger capacity
+    assert tight2.capacity(sb_lib, 2, 36, 3000) > 64
 
 
 def test_per_view_wrapper_matches_fused_path(cuda, sb_lib):

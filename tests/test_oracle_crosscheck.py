@@ -97,3 +97,54 @@ def test_wrapper_matches_manual_three_calls():
     assert torch.allclose(rgbs[1], img.clamp(max=1.0), atol=1e-6)
     assert torch.allclose(alphas[1][..., 0], alpha, atol=1e-6)
     assert float(rgbs[1].max()) <= 1.0
+
+
+def test_tile_lists_equal_the_global_sort_and_tile_subsets_composite_alike():
+    """oracle.tile_lists (tile-by-tile statement used for frames too large for the CPU sort) against
+    bin_and_sort_gaussians, and rasterize_forward(tiles=...) against the full frame."""
+    xys, depths, radii, conics, tiles_hit, colors, opac, bg, k = _projected(900, (96, 80), 5, 16, mult=0.8,
+                                                                           dtype=torch.float32)
+    xys[:30] = xys[0]; depths[:30] = depths[0]; radii[:30] = radii[0]            # exact depth ties -> id order
+    tb = ((k["W"] + 15) // 16, (k["H"] + 15) // 16, 1)
+    from oracle.ref_torch import _tile_bbox
+    mnx, mxx, mny, mxy = _tile_bbox(xys[:, 0], xys[:, 1], radii.float(), tb[0], tb[1], 16)
+    tiles_hit = torch.where(radii > 0, (mxx - mnx) * (mxy - mny), torch.zeros_like(mnx)).to(torch.int32)
+    ni, cum = R.compute_cumulative_intersects(tiles_hit)
+    _, _, _, gids_ref, bins_ref = R.bin_and_sort_gaussians(900, ni, xys, depths, radii, cum, tb, 16)
+    subset = [0, 3, 7, 11, 17, 22, 29]
+    gids, bins = R.tile_lists(xys, depths, radii, tb, 16, subset)
+    for t in subset:
+        a = gids[int(bins[t, 0]):int(bins[t, 1])]
+        b = gids_ref[int(bins_ref[t, 0]):int(bins_ref[t, 1])]
+        assert torch.equal(a, b), f"tile {t}"
+    full = R.rasterize_forward(xys, conics, colors, opac, gids_ref, bins_ref, k["H"], k["W"], 16, bg)
+    part = R.rasterize_forward(xys, conics, colors, opac, gids, bins, k["H"], k["W"], 16, bg, tiles=subset)
+    part2 = R.rasterize_forward(xys, conics, colors, opac, gids_ref, bins_ref, k["H"], k["W"], 16, bg, tiles=subset)
+    for t in subset:
+        ty, tx = divmod(t, tb[0])
+        sl = (slice(ty * 16, min(ty * 16 + 16, k["H"])), slice(tx * 16, min(tx * 16 + 16, k["W"])))
+        assert torch.equal(full[0][sl], part[0][sl]) and torch.equal(full[1][sl], part[1][sl])
+        assert torch.equal(full[0][sl], part2[0][sl])
+
+
+def test_wrapper_edge_paths_of_the_reference():
+    """gs_utils.py:47-51 (a quaternion that does not normalise to unit length becomes (0,0,0,1)) and
+    :72-76 (a mean on the camera centre): same image as with the substituted values, finite gradients,
+    none for the substituted quaternion."""
+    gs = synth.shell_scene(300, 1, seed=3, scale_mult=0.8)
+    cams = synth.orbit_cameras(1, 48, 48)
+    gs["quats"][5] = 0.0
+    gs["quats"][6] = float("nan")
+    gs["means"][7] = cams["camera_to_worlds"][0][:3, 3]
+    kw = {k: cams[k] for k in ("cx", "cy", "fx", "fy", "width", "height", "background_color")}
+    raw = {k: v.clone().requires_grad_() for k, v in gs.items()}
+    rgb, _ = R.render_view(raw, cams["camera_to_worlds"][0], **kw)
+    gs2 = {k: v.clone() for k, v in gs.items()}
+    gs2["quats"][5] = torch.tensor([0.0, 0.0, 0.0, 1.0]); gs2["quats"][6] = torch.tensor([0.0, 0.0, 0.0, 1.0])
+    rgb2, _ = R.render_view(gs2, cams["camera_to_worlds"][0], **kw)
+    assert torch.isfinite(rgb).all() and torch.equal(rgb, rgb2)
+    rgb.sum().backward()
+    for name, p in raw.items():
+        assert torch.isfinite(p.grad).all(), name
+    assert float(raw["quats"].grad[5].abs().sum()) == 0.0 and float(raw["quats"].grad[6].abs().sum()) == 0.0
+    assert float(raw["features_rest"].grad[7].abs().sum()) == 0.0          # depth 0: culled, never drawn

@@ -84,7 +84,8 @@ SB_API int sb_project_bwd(int num_views, int n, const float* means, const float*
                    float* v_scales, float* v_quats, float* v_viewmats, sb_stream_t stream);
 
 /* ---- a5: gsplat.utils.compute_cumulative_intersects ------------------------------------
- * inclusive int32 prefix sum over the flattened (V*N) tile counts. */
+ * inclusive int32 prefix sum over the flattened (V*N) tile counts (single-pass scan with
+ * decoupled look-back, csrc/radix_sort.cu; `temp` is its look-back state). */
 SB_API size_t sb_cumsum_temp_bytes(int count);
 SB_API int sb_cumsum_i32(int count, const int* in, int* out, void* temp, size_t temp_bytes,
                   sb_stream_t stream);
@@ -122,7 +123,19 @@ SB_API int sb_map_gaussian_to_tiles_ordered(int num_views, int n, const float* x
                                      const float* depths, const int* radii, const int* order,
                                      const int* cum_tiles_hit_ordered, int tiles_x, int tiles_y,
                                      int block_width, uint32_t* tile_ids, int* gaussian_ids,
-                                     sb_stream_t stream);
+                                     uint32_t* digit_hist, int hist_passes, sb_stream_t stream);
+/* digit_hist (may be NULL): [hist_passes][256] uint32, zero-filled by the caller; the emission adds, for each
+ * of the hist_passes (1..4) low bytes of the tile index, the number of emitted pairs per byte value -- the
+ * histograms sb_sort_tiles_global would otherwise take with a read of its own.
+ * sb_sort_tiles_global: stable sort of the (tile index, Gaussian id) pairs on the tile index
+ * (num_tiles_total = V*T distinct values), keeping ONLY the sorted ids (the key is implied by the bin); the
+ * last sweep counts the pairs per tile, and a single-pass scan + one elementwise kernel inside the same call
+ * turn the counts into tile_bins (num_tiles_total, 2), (0,0) for empty tiles.
+ * Temp: sb_sort_tiles_global_temp_bytes(count, num_tiles_total). */
+SB_API size_t sb_sort_tiles_global_temp_bytes(int count, int num_tiles_total);
+SB_API int sb_sort_tiles_global(int count, int num_tiles_total, const uint32_t* tile_ids, const int* gaussian_ids,
+                         int* gaussian_ids_sorted, int* tile_bins, const uint32_t* digit_hist, void* temp,
+                         size_t temp_bytes, sb_stream_t stream);
 SB_API size_t sb_sort32_temp_bytes(int count);
 SB_API int sb_sort_pairs32(int count, int end_bit, const uint32_t* keys_in, const int* vals_in,
                     uint32_t* keys_out, int* vals_out, void* temp, size_t temp_bytes, sb_stream_t stream);
@@ -130,7 +143,8 @@ SB_API int sb_tile_bin_edges32(int count, const uint32_t* tile_ids_sorted, int n
                         sb_stream_t stream);
 
 /* ---- a7: the 64-bit (tile|depth) key sort (upstream: torch.sort + torch.gather) --------
- * stable LSD radix sort of (key, value) pairs over key bits [0, end_bit). */
+ * stable LSD radix sort of (key, value) pairs over key bits [0, end_bit): hand-written one-sweep passes
+ * (8-bit digits, decoupled look-back, csrc/radix_sort.cu), count < 2^30. */
 SB_API size_t sb_sort_temp_bytes(int num_intersects);
 SB_API int sb_sort_pairs_range(int count, int begin_bit, int end_bit, const int64_t* keys_in,
                         const int* vals_in, int64_t* keys_out, int* vals_out, void* temp,

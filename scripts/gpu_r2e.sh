@@ -1,0 +1,22 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_sort.py tests/test_gpu_parity.py -m gpu -x -q > gpurun_out/r2e_pytest_sort.log 2>&1
+echo "sort+parity pytest rc=$?"; tail -3 gpurun_out/r2e_pytest_sort.log
+timeout 300 python scripts/bench_sort.py 2>&1 | tail -1 | tee gpurun_out/r2e_sort_bench.json | python -c "
+import json,sys
+d=json.loads(sys.stdin.read())
+for k,v in d.items(): print('  ',k,{a:(round(b,3) if isinstance(b,float) else b) for a,b in v.items()})
+"
+SORT_BENCH_ONLY=config4_47M ncu --metrics gpu__time_duration.sum --clock-control none -c 120 --csv --log-file gpurun_out/r2e_sort_launches.csv python scripts/bench_sort.py > gpurun_out/r2e_sort_ncu.log 2>&1; python - <<PY
+import csv
+rows=[r for r in csv.reader(open("gpurun_out/r2e_sort_launches.csv")) if len(r)>10]
+hdr=rows[0]; ki=hdr.index("Kernel Name"); vi=hdr.index("Metric Value")
+from collections import defaultdict
+agg=defaultdict(list)
+for r in rows[1:]:
+    try: agg[r[ki][:70]].append(float(r[vi].replace(",","")))
+    except: pass
+for k,v in agg.items():
+    if "sb::" in k or "cub::" in k: print(len(v), round(sum(v)/len(v)/1000,1),"us", k)
+PY
+SORT_BENCH_ONLY=config4_47M ncu --set full --clock-control none --import-source on -k regex:onesweep_kernel -s 6 -c 1 -o gpurun_out/r2e_onesweep -f python scripts/bench_sort.py > gpurun_out/r2e_sort_ncu_full.log 2>&1

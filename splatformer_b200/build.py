@@ -33,6 +33,7 @@ UNITS = {
     "project_fwd.cu": ["--fmad=false"],
     "project_bwd.cu": ["--fmad=false"],
     "tiles.cu": [],
+    "radix_sort.cu": [],
     "tile_sort.cu": [],
     "raster_fwd.cu": [],
     "raster_bwd.cu": [],

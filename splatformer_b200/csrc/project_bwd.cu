@@ -96,29 +96,41 @@ __global__ void __launch_bounds__(kProjBwdBlock) project_bwd_kernel(
 // Fused multi-view backward: counterpart of views_project_fwd_kernel.  Reads the packed gradient
 // record [M1x M1y M2xx M2xy | M2yy M0 v_r v_g | v_b ...] the raster backward accumulated for every
 // (view, Gaussian), recomputes the forward record (this TU is built with --fmad=false like the
-// forward, so `valid` is reproduced exactly) and sums the VJPs over the views.
+// forward, so `valid` is reproduced exactly) and sums the VJPs over the views in registers: four lanes
+// share a Gaussian and are joined with two shuffle steps, so every gradient is written once.
 //
 // Most (view, Gaussian) records are all-zero: a Gaussian behind the opaque front of the object never
-// reaches a pixel before that pixel's transmittance runs out, and a culled one is never touched.  A
-// thread that owned fixed (Gaussian, view) pairs would still run the ~1000-instruction recompute +
-// VJP whenever ANY lane of its warp had work.  So every warp first scans the records of its 8
-// Gaussians x V views (coalesced: 8 consecutive 48-byte records per view), compacts the non-zero
-// pairs into a list in shared memory with one ballot per 32 pairs, and then the lanes take pairs from
-// that list -- all 32 lanes busy until the list runs out.  The per-Gaussian sums live in shared memory
-// (red.shared.add.f32; the SH block is the very buffer that is staged out to v_color_src / v_color_rest
-// afterwards), so no thread carries 48 accumulators in registers across the loop.
+// reaches a pixel before that pixel's transmittance runs out, and a culled one is never touched.  With
+// fixed (lane, view) pairs the ~1000-instruction recompute + VJP still ran whenever ANY lane of the warp
+// had work.  So every warp first scans the records of its 8 Gaussians x V views (coalesced: 8 consecutive
+// 48-byte records per view) and compacts, per Gaussian, the views with a non-zero record into a list in
+// shared memory (one ballot per 32 records); then the Gaussian's four lanes walk ITS list, k = lane, lane
+// + 4, ...: the trip count is the longest list / 4 instead of V / 4.
 // ------------------------------------------------------------------------------------------------
 constexpr int kViewsBwdBlock = 128;
 constexpr int kBwdWarps = kViewsBwdBlock / 32;
-constexpr int kBwdRowsPerWarp = 8;                            // Gaussians whose pairs one warp compacts together
+constexpr int kViewLanesB = 4;                                // lanes sharing one Gaussian
+constexpr int kBwdRowsPerWarp = 32 / kViewLanesB;             // Gaussians per warp (8)
 constexpr int kViewsBwdRows = kBwdWarps * kBwdRowsPerWarp;    // Gaussians per block
 constexpr int kBwdViewChunk = 64;                             // views scanned per compaction round (list capacity)
-constexpr int kBwdAcc = 20;    // per-Gaussian sums: v_mean[3] v_scale[3] v_quat[4] v_op | op | v_rgb[3] pad | rgb[3] pad
-constexpr int kBwdPar = 12;    // per-Gaussian inputs: mean[3] scale[3] quat[4] |q_raw| pad
 
+__device__ __forceinline__ float sum_view_lanes(float x) {
+  x += __shfl_xor_sync(0xffffffffu, x, 1);
+  x += __shfl_xor_sync(0xffffffffu, x, 2);
+  return x;
+}
+__device__ __forceinline__ float max_view_lanes(float x) {
+  x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 1));
+  x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 2));
+  return x;
+}
+
+// shared memory: [rows][padded row] staging of the SH gradients | [3K][block] per-thread SH sums | counts | lists
 __host__ __device__ inline size_t views_bwd_smem_bytes(int k3_store, bool sh) {
-  return ((sh ? (size_t)kViewsBwdRows * (k3_store | 1) : 0) + (size_t)kViewsBwdRows * (kBwdAcc + kBwdPar)) * sizeof(float) +
-         (size_t)kBwdWarps * kBwdRowsPerWarp * kBwdViewChunk * sizeof(unsigned short);
+  const size_t stage = sh ? (size_t)kViewsBwdRows * (k3_store | 1) * sizeof(float) : 0;
+  const size_t priv = sh ? (size_t)k3_store * kViewsBwdBlock * sizeof(float) : 0;
+  const size_t lists = (size_t)kViewsBwdRows * kBwdViewChunk + (size_t)kViewsBwdRows * sizeof(int);
+  return stage + priv + ((lists + 15) & ~(size_t)15);
 }
 
 template <int DEG>
@@ -135,144 +147,165 @@ __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_projec
   extern __shared__ float smem[];
   constexpr int KU = DEG < 0 ? 1 : (DEG + 1) * (DEG + 1);
   const int row_stride = DEG >= 0 ? padded_row(k3_store) : 0;
-  float* s_sh = smem;                                              // [rows][row_stride]  SH gradient sums
-  float* s_acc = s_sh + kViewsBwdRows * row_stride;                // [rows][kBwdAcc]
-  float* s_par = s_acc + kViewsBwdRows * kBwdAcc;                  // [rows][kBwdPar]
-  unsigned short* s_list = reinterpret_cast<unsigned short*>(s_par + kViewsBwdRows * kBwdPar);
+  // the SH sums of a thread live in shared memory (column threadIdx.x of a [3K][block] array: conflict-free,
+  // private, no atomics) -- 48 accumulators less in registers than the projection chain can spare
+  float* s_priv = smem + kViewsBwdRows * row_stride + threadIdx.x;
+  const int k3u = DEG >= 0 ? KU * 3 : 0;
+  int* s_cnt = reinterpret_cast<int*>(smem + kViewsBwdRows * row_stride + (DEG >= 0 ? k3_store * kViewsBwdBlock : 0));   // [rows]
+  unsigned char* s_list = reinterpret_cast<unsigned char*>(s_cnt + kViewsBwdRows);         // [rows][kBwdViewChunk]
   const int g0 = blockIdx.x * kViewsBwdRows;
   const int nb = min(kViewsBwdRows, n - g0);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-
-  for (int i = threadIdx.x; i < kViewsBwdRows * (row_stride + kBwdAcc); i += kViewsBwdBlock) smem[i] = 0.f;
-  if (threadIdx.x < nb) {
-    // view-independent inputs of the block's Gaussians, activations applied once (gs_utils.py:45-51)
-    const int g = g0 + threadIdx.x;
-    float* par = s_par + threadIdx.x * kBwdPar;
-    par[0] = __ldg(means + 3 * g); par[1] = __ldg(means + 3 * g + 1); par[2] = __ldg(means + 3 * g + 2);
-    float s0 = __ldg(scales + 3 * g), s1 = __ldg(scales + 3 * g + 1), s2 = __ldg(scales + 3 * g + 2);
-    if (flags & kFlagRawScales) { s0 = expf(s0); s1 = expf(s1); s2 = expf(s2); }
-    par[3] = s0; par[4] = s1; par[5] = s2;
-    const float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + g);
+  const int rowi = threadIdx.x / kViewLanesB, sub = threadIdx.x % kViewLanesB;          // work phase: my Gaussian
+  const int g = g0 + rowi;
+  const bool active = rowi < nb;
+  float acc[3] = {0.f, 0.f, 0.f};                      // DEG < 0: the rgb gradient sums
+#pragma unroll
+  for (int i = 0; i < k3u; ++i) s_priv[i * kViewsBwdBlock] = 0.f;
+  {
+    // inactive rows (tail block) read Gaussian n-1 and never find work
+    const int gl = active ? g : n - 1;
+    const float m[3] = {__ldg(means + 3 * gl), __ldg(means + 3 * gl + 1), __ldg(means + 3 * gl + 2)};
+    float s[3] = {__ldg(scales + 3 * gl), __ldg(scales + 3 * gl + 1), __ldg(scales + 3 * gl + 2)};
+    if (flags & kFlagRawScales) { s[0] = expf(s[0]); s[1] = expf(s[1]); s[2] = expf(s[2]); }
+    const float4 q4 = __ldg(reinterpret_cast<const float4*>(quats) + gl);
     float q[4] = {q4.x, q4.y, q4.z, q4.w};
     float qraw = 1.0f;
-    if (flags & kFlagRawQuats) qraw = wrapper_normalise_quat(q);
-    par[6] = q[0]; par[7] = q[1]; par[8] = q[2]; par[9] = q[3]; par[10] = qraw;
-  }
-  __syncthreads();
+    if (flags & kFlagRawQuats) qraw = wrapper_normalise_quat(q);      // gs_utils.py:46-51
+    float am[3] = {0, 0, 0}, as[3] = {0, 0, 0}, aq[4] = {0, 0, 0, 0}, aop = 0.f;
+    float op = 0.f, col0 = 0.f, col1 = 0.f, col2 = 0.f;
 
-  const int rows_w = max(0, min(kBwdRowsPerWarp, nb - warp * kBwdRowsPerWarp));     // this warp's Gaussians
-  const int row0 = warp * kBwdRowsPerWarp;
-  unsigned short* list = s_list + warp * (kBwdRowsPerWarp * kBwdViewChunk);
-  int n_pairs = 0, n_live = 0;
-  for (int vc0 = 0; vc0 < num_views && rows_w > 0; vc0 += kBwdViewChunk) {
-    const int vc = min(kBwdViewChunk, num_views - vc0);
-    // ---- scan: pair p = (view vc0 + p / 8, row p % 8); keep the ones with a non-zero gradient record ----
-    int cnt = 0;
-    const int total = vc * kBwdRowsPerWarp;
-    for (int p0 = 0; p0 < total; p0 += 32) {
-      const int p = p0 + lane;
-      const int r = p & (kBwdRowsPerWarp - 1), vv = p >> 3;
-      bool nz = false;
-      if (p < total && r < rows_w) {
-        const float4* rec = v_packed + 3 * ((size_t)(vc0 + vv) * n + g0 + row0 + r);
-        const float4 a = __ldg(rec), b = __ldg(rec + 1);
-        const float c = __ldg(reinterpret_cast<const float*>(rec + 2));
-        nz = a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f || b.x != 0.f || b.y != 0.f || b.z != 0.f ||
-             b.w != 0.f || c != 0.f;
-      }
-      const unsigned bal = __ballot_sync(0xffffffffu, nz);
-      if (nz) list[cnt + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)p;
-      cnt += __popc(bal);
-    }
-    __syncwarp();
-    n_pairs += total; n_live += cnt;
-    // ---- work: lanes take the live pairs ----
-    for (int k = lane; k < cnt; k += 32) {
-      const int p = list[k];
-      const int r = row0 + (p & (kBwdRowsPerWarp - 1)), v = vc0 + (p >> 3);
-      const float* par = s_par + r * kBwdPar;
-      const float m[3] = {par[0], par[1], par[2]};
-      const float s[3] = {par[3], par[4], par[5]};
-      const float q[4] = {par[6], par[7], par[8], par[9]};
-      const Cam cam = load_cam(cams, v);
-      ProjFwd f;
-      project_fwd_one(m, s, glob, q, cam, img_w, img_h, bw, clip, f);
-      if (!f.valid) continue;                          // (a culled pair's record is never written: not reached)
-      const size_t i = (size_t)v * n + g0 + r;
-      const float4 ga = __ldg(v_packed + 3 * i), gb = __ldg(v_packed + 3 * i + 1);
-      const float gcx = __ldg(reinterpret_cast<const float*>(v_packed + 3 * i + 2));
-      const float4 col = __ldg(packed + 3 * i + 2);       // r, g, b (after the clamp), opacity
-      float vm[3], vs[3], vq[4];
-      float vx, vy, vca, vcb, vcc, vop;
-      moments_to_grads(ga, gb, f.ca, f.cb, f.cc, col.w, vx, vy, vca, vcb, vcc, vop);
-      project_bwd_one(m, s, glob, cam, f, vx, vy, 0.f, vca, vcb, vcc, 0.f, nullptr, vm, vs, vq, nullptr);
-      float* acc = s_acc + r * kBwdAcc;
-#pragma unroll
-      for (int j = 0; j < 3; ++j) { atomicAdd(acc + j, vm[j]); atomicAdd(acc + 3 + j, vs[j]); }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) atomicAdd(acc + 6 + j, vq[j]);
-      atomicAdd(acc + 10, vop);
-      acc[11] = col.w;                                   // view-independent: every writer stores the same value
-      float vr = gb.z, vg = gb.w, vb = gcx;
-      if (DEG >= 0) {
-        // clamp(x + 0.5, min 0): gradient passes where > 0
-        vr = col.x > 0.f ? vr : 0.f; vg = col.y > 0.f ? vg : 0.f; vb = col.z > 0.f ? vb : 0.f;
-        float Y[KU], cp[3];
-        load_campos(cams, campos, v, cp);
-        sh_basis(DEG, m[0] - cp[0], m[1] - cp[1], m[2] - cp[2], Y);
-        float* sh = s_sh + r * row_stride;
-#pragma unroll
-        for (int j = 0; j < KU; ++j) {
-          atomicAdd(sh + 3 * j, Y[j] * vr); atomicAdd(sh + 3 * j + 1, Y[j] * vg); atomicAdd(sh + 3 * j + 2, Y[j] * vb);
+    const int row0 = warp * kBwdRowsPerWarp;                       // scan phase: the warp's first Gaussian
+    const int rows_w = max(0, min(kBwdRowsPerWarp, nb - row0));
+    const int scan_r = lane & (kBwdRowsPerWarp - 1);               // scan phase: lane looks at row scan_r, views lane / 8 + 4 j
+    const unsigned row_mask = 0x01010101u << scan_r;
+    const unsigned lt = (1u << lane) - 1u;
+    int n_scanned = 0, n_live = 0;
+    for (int vc0 = 0; vc0 < num_views; vc0 += kBwdViewChunk) {
+      const int vc = min(kBwdViewChunk, num_views - vc0);
+      // ---- scan: record (view vc0 + p / 8, row p % 8); per row, the views whose record is not all-zero ----
+      int cnt = 0;
+      const int total = vc * kBwdRowsPerWarp;
+      for (int p0 = 0; p0 < total; p0 += 32) {
+        const int p = p0 + lane;
+        const int vv = p >> 3;
+        bool nz = false;
+        if (p < total && scan_r < rows_w) {
+          const float4* rec = v_packed + 3 * ((size_t)(vc0 + vv) * n + g0 + row0 + scan_r);
+          const float4 a = __ldg(rec), b = __ldg(rec + 1);
+          const float c = __ldg(reinterpret_cast<const float*>(rec + 2));
+          nz = a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f || b.x != 0.f || b.y != 0.f || b.z != 0.f ||
+               b.w != 0.f || c != 0.f;
         }
-      } else {
-        atomicAdd(acc + 12, vr); atomicAdd(acc + 13, vg); atomicAdd(acc + 14, vb);
-        acc[16] = col.x; acc[17] = col.y; acc[18] = col.z;     // activated colours (view-independent)
+        const unsigned bal = __ballot_sync(0xffffffffu, nz) & row_mask;
+        if (nz) s_list[(row0 + scan_r) * kBwdViewChunk + cnt + __popc(bal & lt)] = (unsigned char)vv;
+        cnt += __popc(bal);
       }
+      if (lane < kBwdRowsPerWarp) s_cnt[row0 + lane] = cnt;
+      n_scanned += (lane < rows_w) ? vc : 0;
+      n_live += (lane < kBwdRowsPerWarp) ? cnt : 0;
+      __syncwarp();
+      // ---- work: the Gaussian's four lanes walk its list ----
+      const int my_cnt = s_cnt[rowi];
+      const unsigned char* my_list = s_list + rowi * kBwdViewChunk;
+      for (int k = sub; k < my_cnt; k += kViewLanesB) {
+        const int v = vc0 + my_list[k];
+        const Cam cam = load_cam(cams, v);
+        ProjFwd f;
+        project_fwd_one(m, s, glob, q, cam, img_w, img_h, bw, clip, f);
+        if (!f.valid) continue;                        // (a culled pair's record is never written: not reached)
+        const size_t i = (size_t)v * n + gl;
+        const float4 ga = __ldg(v_packed + 3 * i), gb = __ldg(v_packed + 3 * i + 1);
+        const float gcx = __ldg(reinterpret_cast<const float*>(v_packed + 3 * i + 2));
+        const float4 col = __ldg(packed + 3 * i + 2);       // r, g, b (after the clamp), opacity
+        op = col.w; col0 = col.x; col1 = col.y; col2 = col.z;
+        float vm[3], vs[3], vq[4];
+        float vx, vy, vca, vcb, vcc, vop;
+        moments_to_grads(ga, gb, f.ca, f.cb, f.cc, op, vx, vy, vca, vcb, vcc, vop);
+        project_bwd_one(m, s, glob, cam, f, vx, vy, 0.f, vca, vcb, vcc, 0.f, nullptr, vm, vs, vq, nullptr);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) { am[j] += vm[j]; as[j] += vs[j]; }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) aq[j] += vq[j];
+        aop += vop;
+        float vr = gb.z, vg = gb.w, vb = gcx;
+        if (DEG >= 0) {
+          // clamp(x + 0.5, min 0): gradient passes where > 0
+          vr = col.x > 0.f ? vr : 0.f; vg = col.y > 0.f ? vg : 0.f; vb = col.z > 0.f ? vb : 0.f;
+          float Y[KU], cp[3];
+          load_campos(cams, campos, v, cp);
+          sh_basis(DEG, m[0] - cp[0], m[1] - cp[1], m[2] - cp[2], Y);
+#pragma unroll
+          for (int j = 0; j < KU; ++j) {
+            s_priv[(3 * j) * kViewsBwdBlock] += Y[j] * vr;
+            s_priv[(3 * j + 1) * kViewsBwdBlock] += Y[j] * vg;
+            s_priv[(3 * j + 2) * kViewsBwdBlock] += Y[j] * vb;
+          }
+        } else {
+          acc[0] += vr; acc[1] += vg; acc[2] += vb;
+        }
+      }
+      __syncwarp();
     }
-    __syncwarp();
-  }
-  if (stats && lane == 0 && n_pairs > 0) { atomicAdd(stats, n_pairs); atomicAdd(stats + 1, n_live); }
-  __syncthreads();
-
-  // ---- epilogue: chain rule through the activations the kernels applied themselves (gs_utils.py:45-51,54,65) ----
-  if (threadIdx.x < nb) {
-    const int g = g0 + threadIdx.x;
-    const float* acc = s_acc + threadIdx.x * kBwdAcc;
-    const float* par = s_par + threadIdx.x * kBwdPar;
-    float as0 = acc[3], as1 = acc[4], as2 = acc[5];
-    if (flags & kFlagRawScales) { as0 *= par[3]; as1 *= par[4]; as2 *= par[5]; }
-    v_means[3 * g] = acc[0]; v_means[3 * g + 1] = acc[1]; v_means[3 * g + 2] = acc[2];
-    v_scales[3 * g] = as0; v_scales[3 * g + 1] = as1; v_scales[3 * g + 2] = as2;
-    float aq0 = acc[6], aq1 = acc[7], aq2 = acc[8], aq3 = acc[9];
+    if (stats) {
+      n_scanned = __reduce_add_sync(0xffffffffu, n_scanned);
+      n_live = __reduce_add_sync(0xffffffffu, n_live);
+      if (lane == 0 && n_scanned > 0) { atomicAdd(stats, n_scanned); atomicAdd(stats + 1, n_live); }
+    }
+    // join the four view lanes of the Gaussian (op / colour are view-independent: take any lane that saw them)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { am[k] = sum_view_lanes(am[k]); as[k] = sum_view_lanes(as[k]); }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) aq[k] = sum_view_lanes(aq[k]);
+    aop = sum_view_lanes(aop);
+    if (DEG < 0) { acc[0] = sum_view_lanes(acc[0]); acc[1] = sum_view_lanes(acc[1]); acc[2] = sum_view_lanes(acc[2]); }
+    op = max_view_lanes(op);
+    if (DEG < 0 && (flags & kFlagColorSigmoid)) {
+      // colours are in (0, 1) where a view drew the Gaussian and 0 in lanes that saw none
+      col0 = max_view_lanes(col0); col1 = max_view_lanes(col1); col2 = max_view_lanes(col2);
+    }
+    // chain rule through the activations the kernel applied itself (gs_utils.py:45-51,54,65)
+    if (flags & kFlagRawScales) { as[0] *= s[0]; as[1] *= s[1]; as[2] *= s[2]; }
     if (flags & kFlagRawQuats) {
-      // through q / |q| of the wrapper; a substituted quaternion (|q| reported as 0) gets no gradient
-      const float qn = par[10];
-      if (qn > 0.f) {
-        const float d = par[6] * aq0 + par[7] * aq1 + par[8] * aq2 + par[9] * aq3;
-        const float inv = 1.0f / qn;
-        aq0 = (aq0 - par[6] * d) * inv; aq1 = (aq1 - par[7] * d) * inv;
-        aq2 = (aq2 - par[8] * d) * inv; aq3 = (aq3 - par[9] * d) * inv;
-      } else { aq0 = aq1 = aq2 = aq3 = 0.f; }
-    }
-    reinterpret_cast<float4*>(v_quats)[g] = make_float4(aq0, aq1, aq2, aq3);
-    float aop = acc[10];
-    if (flags & kFlagRawOpacities) { const float op = acc[11]; aop *= op * (1.0f - op); }
-    v_opacities[g] = aop;
-    if (DEG < 0) {
-      float c0 = acc[12], c1 = acc[13], c2 = acc[14];
-      if (flags & kFlagColorSigmoid) {
-        c0 *= acc[16] * (1.0f - acc[16]); c1 *= acc[17] * (1.0f - acc[17]); c2 *= acc[18] * (1.0f - acc[18]);
+      // through the wrapper's q / |q|; a substituted quaternion (|q| reported as 0) gets no gradient
+      if (qraw > 0.f) {
+        const float d = q[0] * aq[0] + q[1] * aq[1] + q[2] * aq[2] + q[3] * aq[3];
+        const float inv = 1.0f / qraw;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) aq[k] = (aq[k] - q[k] * d) * inv;
+      } else {
+        aq[0] = aq[1] = aq[2] = aq[3] = 0.f;
       }
-      v_color_src[3 * g] = c0; v_color_src[3 * g + 1] = c1; v_color_src[3 * g + 2] = c2;
+    }
+    if (flags & kFlagRawOpacities) aop *= op * (1.0f - op);
+    if (DEG < 0 && (flags & kFlagColorSigmoid)) {
+      acc[0] *= col0 * (1.0f - col0); acc[1] *= col1 * (1.0f - col1); acc[2] *= col2 * (1.0f - col2);
+    }
+    if (active && sub == 0) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { v_means[3 * g + k] = am[k]; v_scales[3 * g + k] = as[k]; }
+      reinterpret_cast<float4*>(v_quats)[g] = make_float4(aq[0], aq[1], aq[2], aq[3]);
+      v_opacities[g] = aop;
+      if (DEG < 0) { v_color_src[3 * g] = acc[0]; v_color_src[3 * g + 1] = acc[1]; v_color_src[3 * g + 2] = acc[2]; }
     }
   }
   if (DEG >= 0) {
+    // join the four lanes' SH sums into the staging rows (lane `sub` takes every fourth coefficient)
+    __syncwarp();
+    if (active) {
+      const float* col = smem + kViewsBwdRows * row_stride + rowi * kViewLanesB;
+      for (int i = sub; i < k3u; i += kViewLanesB) {
+        const float* c = col + i * kViewsBwdBlock;
+        smem[rowi * row_stride + i] = (c[0] + c[1]) + (c[2] + c[3]);
+      }
+      for (int i = k3u + sub; i < k3_store; i += kViewLanesB) smem[rowi * row_stride + i] = 0.f;   // (bases not used)
+    }
+    __syncthreads();
     if (v_color_rest) {
-      stage_rows_out(s_sh, v_color_src + (size_t)g0 * 3, nb, 3, kViewsBwdBlock, row_stride, 0);
-      if (k3_store > 3) stage_rows_out(s_sh, v_color_rest + (size_t)g0 * (k3_store - 3), nb, k3_store - 3, kViewsBwdBlock, row_stride, 3);
+      stage_rows_out(smem, v_color_src + (size_t)g0 * 3, nb, 3, kViewsBwdBlock, row_stride, 0);
+      if (k3_store > 3) stage_rows_out(smem, v_color_rest + (size_t)g0 * (k3_store - 3), nb, k3_store - 3, kViewsBwdBlock, row_stride, 3);
     } else {
-      stage_rows_out(s_sh, v_color_src + (size_t)g0 * k3_store, nb, k3_store, kViewsBwdBlock, row_stride, 0);
+      stage_rows_out(smem, v_color_src + (size_t)g0 * k3_store, nb, k3_store, kViewsBwdBlock, row_stride, 0);
     }
   }
 }

@@ -2,8 +2,7 @@
 // gsplat.utils.{compute_cumulative_intersects, map_gaussian_to_intersects, bin_and_sort_gaussians,
 // get_tile_bin_edges}, reached from gsplat.rasterize_gaussians at
 // /root/reference/utils/gs_utils.py:96-109).  All integer work, bit-exact by construction.
-#include <cub/device/device_radix_sort.cuh>
-#include <cub/device/device_scan.cuh>
+// The sort and the prefix sum themselves live in radix_sort.cu.
 #include "sb_common.cuh"
 
 namespace sb {
@@ -16,12 +15,22 @@ constexpr int kCoopTiles = 8;
 
 // COMPACT: the key is the 32-bit tile index alone (depth-ordered emission: the depth is already encoded in
 // the position), stored through the same pointer reinterpreted as uint32.
+// COMPACT with digit_hist: the kernel also counts, for each of the `hist_passes` low bytes of the tile index,
+// how many emitted pairs carry each byte value ([hist_passes][256], zero on entry) -- the digit histograms the
+// one-sweep radix sort needs, taken here while the keys are in registers instead of by another read.
 template <bool COMPACT>
 __global__ void __launch_bounds__(256) map_isect_kernel(
     int num_views, int n, const float* __restrict__ xys, int xy_stride, const float* __restrict__ depths,
     const int* __restrict__ radii, const int* __restrict__ cum, int tiles_x, int tiles_y, int bw,
-    int64_t* __restrict__ keys, int* __restrict__ gids, const int* __restrict__ order) {
+    int64_t* __restrict__ keys, int* __restrict__ gids, const int* __restrict__ order,
+    unsigned* __restrict__ digit_hist, int hist_passes) {
   uint32_t* keys32 = reinterpret_cast<uint32_t*>(keys);
+  __shared__ unsigned s_hist[4][256];
+  const bool do_hist = COMPACT && digit_hist != nullptr;
+  if (do_hist) {
+    for (int i = threadIdx.x; i < hist_passes * 256; i += 256) (&s_hist[0][0])[i] = 0u;
+    __syncthreads();
+  }
   // slot j of the emission order handles (view, Gaussian) index i = order[j] (identity without `order`);
   // cum is the prefix sum of the tile counts in emission order
   const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;
@@ -52,6 +61,10 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
       const int64_t t = tile0 + (int64_t)(min_y + ky) * tiles_x + (min_x + kx);
       if (COMPACT) keys32[k + e] = (uint32_t)t; else keys[k + e] = (t << 32) | depth_bits;
       gids[k + e] = g;
+      if (do_hist) {
+        // (lanes walk different Gaussians here: their tiles are unrelated, plain shared atomics)
+        for (int p = 0; p < hist_passes; ++p) atomicAdd(&s_hist[p][((uint32_t)t >> (8 * p)) & 255u], 1u);
+      }
     }
   }
   unsigned big = __ballot_sync(0xffffffffu, total > kCoopTiles);
@@ -64,11 +77,36 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
     const size_t s_k = __shfl_sync(0xffffffffu, (unsigned long long)k, src);
     const int64_t s_depth = __shfl_sync(0xffffffffu, (long long)depth_bits, src);
     const int64_t s_tile0 = __shfl_sync(0xffffffffu, (long long)tile0, src);
-    for (int e = lane; e < s_total; e += 32) {
+    for (int e0 = 0; e0 < s_total; e0 += 32) {
+      const int e = e0 + lane;
+      const bool on = e < s_total;
       const int ky = e / s_nx, kx = e - ky * s_nx;
       const int64_t t = s_tile0 + (int64_t)(s_min_y + ky) * tiles_x + (s_min_x + kx);
-      if (COMPACT) keys32[s_k + e] = (uint32_t)t; else keys[s_k + e] = (t << 32) | s_depth;
-      gids[s_k + e] = s_g;
+      if (on) {
+        if (COMPACT) keys32[s_k + e] = (uint32_t)t; else keys[s_k + e] = (t << 32) | s_depth;
+        gids[s_k + e] = s_g;
+      }
+      if (do_hist) {
+        // consecutive lanes = consecutive tiles of a row: the high bytes usually coincide across the warp -- one
+        // vote finds that out and lane 0 adds the whole group; otherwise plain shared atomics (no MATCH.ANY,
+        // see radix_sort.cu)
+        for (int p = 0; p < hist_passes; ++p) {
+          const unsigned d = ((uint32_t)t >> (8 * p)) & 255u;
+          const unsigned d0 = __shfl_sync(0xffffffffu, d, 0);
+          if (__all_sync(0xffffffffu, on && d == d0)) {
+            if (lane == 0) atomicAdd(&s_hist[p][d], 32u);
+          } else if (on) {
+            atomicAdd(&s_hist[p][d], 1u);
+          }
+        }
+      }
+    }
+  }
+  if (do_hist) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < hist_passes * 256; i += 256) {
+      const unsigned c = (&s_hist[0][0])[i];
+      if (c) atomicAdd(digit_hist + i, c);
     }
   }
 }
@@ -121,21 +159,6 @@ __global__ void __launch_bounds__(256) bin_edges32_kernel(int count, const uint3
 
 }  // namespace sb
 
-extern "C" size_t sb_cumsum_temp_bytes(int count) {
-  size_t bytes = 0;
-  cub::DeviceScan::InclusiveSum(nullptr, bytes, (const int*)nullptr, (int*)nullptr, count);
-  return bytes;
-}
-
-extern "C" int sb_cumsum_i32(int count, const int* in, int* out, void* temp, size_t temp_bytes,
-                             sb_stream_t stream) {
-  if (count < 0) return SB_ERR_BAD_ARG;
-  if (count == 0) return 0;
-  size_t need = sb_cumsum_temp_bytes(count);
-  if (temp_bytes < need) return SB_ERR_TEMP_TOO_SMALL;
-  return (int)cub::DeviceScan::InclusiveSum(temp, temp_bytes, in, out, count, (cudaStream_t)stream);
-}
-
 extern "C" int sb_map_gaussian_to_intersects(int num_views, int n, const float* xys, int xys_stride,
                                              const float* depths, const int* radii,
                                              const int* cum_tiles_hit, int tiles_x, int tiles_y,
@@ -147,7 +170,7 @@ extern "C" int sb_map_gaussian_to_intersects(int num_views, int n, const float* 
   if (total == 0) return 0;
   sb::map_isect_kernel<false><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit, tiles_x, tiles_y, block_width, isect_ids,
-      gaussian_ids, nullptr);
+      gaussian_ids, nullptr, nullptr, 0);
   SB_RETURN_LAST();
 }
 
@@ -162,7 +185,7 @@ extern "C" int sb_map_gaussian_to_intersects_ordered(int num_views, int n, const
   if (total == 0) return 0;
   sb::map_isect_kernel<false><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit_ordered, tiles_x, tiles_y, block_width, isect_ids,
-      gaussian_ids, order);
+      gaussian_ids, order, nullptr, 0);
   SB_RETURN_LAST();
 }
 
@@ -170,32 +193,16 @@ extern "C" int sb_map_gaussian_to_tiles_ordered(int num_views, int n, const floa
                                                 const float* depths, const int* radii, const int* order,
                                                 const int* cum_tiles_hit_ordered, int tiles_x, int tiles_y,
                                                 int block_width, uint32_t* tile_ids, int* gaussian_ids,
-                                                sb_stream_t stream) {
-  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || xys_stride < 2 || (xys_stride & 1) || !order)
+                                                uint32_t* digit_hist, int hist_passes, sb_stream_t stream) {
+  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || xys_stride < 2 || (xys_stride & 1) || !order ||
+      (digit_hist && (hist_passes < 1 || hist_passes > 4)))
     return SB_ERR_BAD_ARG;
   const size_t total = (size_t)num_views * n;
   if (total == 0) return 0;
   sb::map_isect_kernel<true><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit_ordered, tiles_x, tiles_y, block_width,
-      reinterpret_cast<int64_t*>(tile_ids), gaussian_ids, order);
+      reinterpret_cast<int64_t*>(tile_ids), gaussian_ids, order, digit_hist, hist_passes);
   SB_RETURN_LAST();
-}
-
-extern "C" size_t sb_sort32_temp_bytes(int count) {
-  size_t bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const int*)nullptr,
-                                  (int*)nullptr, count, 0, 32);
-  return bytes;
-}
-
-extern "C" int sb_sort_pairs32(int count, int end_bit, const uint32_t* keys_in, const int* vals_in,
-                               uint32_t* keys_out, int* vals_out, void* temp, size_t temp_bytes,
-                               sb_stream_t stream) {
-  if (count < 0 || end_bit < 1 || end_bit > 32) return SB_ERR_BAD_ARG;
-  if (count == 0) return 0;
-  if (temp_bytes < sb_sort32_temp_bytes(count)) return SB_ERR_TEMP_TOO_SMALL;
-  return (int)cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, count, 0,
-                                              end_bit, (cudaStream_t)stream);
 }
 
 extern "C" int sb_tile_bin_edges32(int count, const uint32_t* tile_ids_sorted, int num_tiles_total, int* tile_bins,
@@ -222,33 +229,6 @@ extern "C" int sb_gather_i32(int count, const int* src, const int* index, int* d
   if (count == 0) return 0;
   sb::gather_i32_kernel<<<sb::ceil_div(count, 256), 256, 0, (cudaStream_t)stream>>>(count, src, index, dst);
   SB_RETURN_LAST();
-}
-
-extern "C" size_t sb_sort_temp_bytes(int num_intersects) {
-  size_t bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const int64_t*)nullptr, (int64_t*)nullptr,
-                                  (const int*)nullptr, (int*)nullptr, num_intersects, 0, 64);
-  return bytes;
-}
-
-extern "C" int sb_sort_pairs(int num_intersects, int end_bit, const int64_t* keys_in,
-                             const int* vals_in, int64_t* keys_out, int* vals_out, void* temp,
-                             size_t temp_bytes, sb_stream_t stream) {
-  if (num_intersects < 0 || end_bit < 1 || end_bit > 64) return SB_ERR_BAD_ARG;
-  if (num_intersects == 0) return 0;
-  if (temp_bytes < sb_sort_temp_bytes(num_intersects)) return SB_ERR_TEMP_TOO_SMALL;
-  return (int)cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out,
-                                              num_intersects, 0, end_bit, (cudaStream_t)stream);
-}
-
-extern "C" int sb_sort_pairs_range(int count, int begin_bit, int end_bit, const int64_t* keys_in,
-                                   const int* vals_in, int64_t* keys_out, int* vals_out, void* temp,
-                                   size_t temp_bytes, sb_stream_t stream) {
-  if (count < 0 || begin_bit < 0 || end_bit <= begin_bit || end_bit > 64) return SB_ERR_BAD_ARG;
-  if (count == 0) return 0;
-  if (temp_bytes < sb_sort_temp_bytes(count)) return SB_ERR_TEMP_TOO_SMALL;
-  return (int)cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, count,
-                                              begin_bit, end_bit, (cudaStream_t)stream);
 }
 
 extern "C" int sb_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted,

@@ -14,8 +14,12 @@ synchronisation: the tile-segment binning reports "a tile overflowed its segment
 device writes into pinned host memory, and that flag is only looked at when the backward starts (by
 then the device is long past the point that produced it; the forward rasteriser is still running, so
 the GPU never waits for the host).  On the rare overflow the forward is replayed right there with the
-global sort, overwriting the image / loss buffers in place, and the backward continues on the
-corrected state.  Without autograd (evaluation) the flag is read right after the forward.
+global sort, overwriting the image / loss-sum buffers in place, and the backward continues on the
+corrected state (tensors the caller DERIVED from the outputs before calling backward keep the values of
+the truncated pass -- for that one step the logged loss is off, the gradients are not).  The flag is read
+right after the forward -- one synchronisation -- when nothing will come back to repair the pass
+(no autograd: evaluation) and on the FIRST call of a (views, tiles, Gaussians) shape through a plan, which
+is where a shape that does not suit the tile segments at all (configs 4 and 5) is found out.
 """
 from __future__ import annotations
 
@@ -135,6 +139,32 @@ class RenderPlan:
         self.pending: List[_Totals] = []
         self.last: Optional[_Totals] = None
         self.replays = 0
+        self.seen: set = set()               # shapes whose first call (read synchronously) is behind us
+        self._slots: List[Tensor] = []       # pinned (2,) int32 landing buffers of the totals, recycled
+        self._slot_users: List[Optional[_Totals]] = []
+
+    def host_slot(self, totals_factory) -> "_Totals":
+        """A pinned landing buffer for a pass's totals.  Allocating pinned memory per step would cost a
+        cudaHostAlloc whenever the host runs ahead of the device (the caching host allocator cannot recycle a
+        block whose copy is still in flight), so the plan keeps a small ring and reuses a slot once its totals
+        have been read; if every slot is still in flight the oldest one is waited for."""
+        idx = None
+        for i, user in enumerate(self._slot_users):
+            if user is None or user.ready():
+                idx = i
+                break
+        if idx is None and len(self._slots) < 16:
+            self._slots.append(torch.zeros(2, dtype=I32).pin_memory())
+            self._slot_users.append(None)
+            idx = len(self._slots) - 1
+        if idx is None:
+            idx = 0
+        prev = self._slot_users[idx]
+        if prev is not None:
+            prev.read()                      # (copies the two ints out of the slot before it is overwritten)
+        t = totals_factory(self._slots[idx])
+        self._slot_users[idx] = t
+        return t
 
     def capacity(self, lib, v: int, num_tiles: int, n: int) -> int:
         """Segment capacity for the tile sort, or 0 to use the global sort."""
@@ -323,16 +353,18 @@ class _Pass:
                 p(totals, I32, "totals"), self.n, self.tiles_x, p(self.packed, F32, "packed"),
                 p(self.rect_ids, I32, "rect_ids"), p(self.rect_counts, I32, "rect_counts"),
                 self.st), "sb_sort_tiles")
-        host_totals = torch.empty(2, dtype=I32, pin_memory=True)
-        host_totals.copy_(totals, non_blocking=True)
-        ready = torch.cuda.Event()
-        ready.record()
+        def landed(host_totals):
+            host_totals.copy_(totals, non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record()
+            return _Totals(host_totals, ready, (v, num_tiles, self.n), plan)
+        result = plan.host_slot(landed)
         # the raster kernel is enqueued optimistically: the device produced the flag BEFORE it starts
         if use_rect:
             self.raster_rect(view_has, work[:1])
         else:
             self.raster_tiles(view_has)
-        return _Totals(host_totals, ready, (v, num_tiles, self.n), plan)
+        return result
 
     def run_global(self, plan: RenderPlan, projected: bool) -> _Totals:
         """Very deep tiles / many tiles per Gaussian: depth pre-order of the Gaussians, emission in that
@@ -419,8 +451,12 @@ class _RenderViews(Function):
             cap = plan.capacity(lib, v, ps.num_tiles, n)
             if cap:
                 totals = ps.run_segments(cap, plan)
-                if not training:
-                    # evaluation: nothing will come back to repair an overflowed pass, look right away
+                key = (v, ps.num_tiles, n)
+                first = key not in plan.seen
+                plan.seen.add(key)
+                if not training or first:
+                    # evaluation (nothing will come back to repair an overflowed pass) or a shape this plan has
+                    # not seen yet: look right away
                     if totals.read()[1]:
                         plan.replays += 1
                         totals = ps.run_global(plan, projected=True)

@@ -90,6 +90,39 @@ def sort_isects(isect_ids: Tensor, gaussian_ids: Tensor, num_tiles_total: int) -
     return keys_out, vals_out
 
 
+def sort_pairs32(keys: Tensor, vals: Tensor, end_bit: int = 32) -> Tuple[Tensor, Tensor]:
+    """Stable sort of (uint32 key stored as int32, int32 value) pairs on the low `end_bit` key bits."""
+    lib = _abi.load()
+    n = keys.numel()
+    keys_out, vals_out = torch.empty_like(keys), torch.empty_like(vals)
+    if n == 0:
+        return keys_out, vals_out
+    tmp = _scratch(lib.sb_sort32_temp_bytes(n), keys.device)
+    _abi.check(lib.sb_sort_pairs32(n, end_bit, _abi.ptr(keys, torch.int32, "keys"), _abi.ptr(vals, torch.int32, "vals"),
+                                   _abi.ptr(keys_out, torch.int32, "keys_out"), _abi.ptr(vals_out, torch.int32, "vals_out"),
+                                   _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()), "sb_sort_pairs32")
+    return keys_out, vals_out
+
+
+def sort_tile_pairs(tile_ids: Tensor, gaussian_ids: Tensor, num_tiles_total: int) -> Tuple[Tensor, Tensor]:
+    """The fused path's tile-index sort on its own: (tile index, id) pairs -> ids sorted stably by tile, and
+    tile_bins (num_tiles_total, 2).  The sort reads the keys once for its digit histograms here (inside
+    bin_depth_ordered the emission kernel supplies them)."""
+    lib = _abi.load()
+    n = tile_ids.numel()
+    dev = tile_ids.device
+    out = torch.empty_like(gaussian_ids)
+    bins = torch.empty(num_tiles_total, 2, dtype=torch.int32, device=dev)
+    tmp = _scratch(lib.sb_sort_tiles_global_temp_bytes(n, num_tiles_total), dev)
+    _abi.check(lib.sb_sort_tiles_global(n, num_tiles_total, _abi.ptr(tile_ids, torch.int32, "tile_ids"),
+                                        _abi.ptr(gaussian_ids, torch.int32, "gaussian_ids"),
+                                        _abi.ptr(out, torch.int32, "gaussian_ids_sorted"),
+                                        _abi.ptr(bins, torch.int32, "tile_bins"), None,
+                                        _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()),
+               "sb_sort_tiles_global")
+    return out, bins
+
+
 def get_tile_bin_edges(num_intersects: int, isect_ids_sorted: Tensor, tile_bounds,
                        num_views: int = 1) -> Tensor:
     lib = _abi.load()
@@ -119,8 +152,9 @@ def bin_depth_ordered(num_views: int, n: int, xys: Tensor, xys_stride: int, dept
     depth pre-order of the V*N Gaussians (a small sort) -> emission in that order -> stable radix sort
     over the TILE bits only.  The emitted keys are already ascending in depth inside every tile, so the
     big sort needs 2 radix passes over bits [32, 32 + bits(V*T)) instead of 6 over the whole key.
-    compact=True carries only the uint32 tile index through the big sort (8 bytes per pair instead of 12)
-    and returns the sorted tile indices in place of the 64-bit keys.
+    compact=True carries only the uint32 tile index through the big sort (8 bytes per pair instead of 12),
+    whose last sweep keeps just the sorted ids and counts the pairs per tile (no sorted keys are returned:
+    None in their place).
     Returns (num_intersects, isect_ids_sorted, gaussian_ids_sorted, tile_bins, last cumulative count per view)."""
     lib = _abi.load()
     dev = depths.device
@@ -150,39 +184,44 @@ def bin_depth_ordered(num_views: int, n: int, xys: Tensor, xys_stride: int, dept
     kdt = torch.int32 if compact else I64              # int32 storage for the uint32 tile indices
     isect_ids = torch.empty(num_intersects, dtype=kdt, device=dev)
     gaussian_ids = torch.empty(num_intersects, dtype=I32, device=dev)
-    keys_out, vals_out = torch.empty_like(isect_ids), torch.empty_like(gaussian_ids)
+    vals_out = torch.empty_like(gaussian_ids)
+    # emission is view-major (the view is the top of the pre-order key): offsets at the view boundaries
+    view_ends = cum.view(num_views, n)[:, -1] if total > 0 else cum
+    if compact:
+        # tile-index sort that keeps only the sorted ids: the emission counts the digit histograms while the
+        # keys are in registers, the last sweep counts the pairs per tile, a one-CTA scan turns them into bins
+        passes = (tile_bits + 7) // 8
+        digit_hist = torch.zeros(passes * 256, dtype=I32, device=dev)
+        tile_bins = torch.empty(tiles_total, 2, dtype=I32, device=dev)
+        if num_intersects > 0:
+            _abi.check(lib.sb_map_gaussian_to_tiles_ordered(
+                num_views, n, _abi.ptr(xys, F32, "xys"), xys_stride, _abi.ptr(depths, F32, "depths"),
+                _abi.ptr(radii, I32, "radii"), _abi.ptr(order, I32, "order"), _abi.ptr(cum, I32, "cum_tiles_hit"),
+                tiles_x, tiles_y, block_width, _abi.ptr(isect_ids, kdt, "tile_ids"),
+                _abi.ptr(gaussian_ids, I32, "gaussian_ids"), _abi.ptr(digit_hist, I32, "digit_hist"), passes,
+                _abi.stream()), "sb_map_gaussian_to_tiles_ordered")
+        tmp = _scratch(lib.sb_sort_tiles_global_temp_bytes(num_intersects, tiles_total), dev)
+        _abi.check(lib.sb_sort_tiles_global(
+            num_intersects, tiles_total, _abi.ptr(isect_ids, kdt, "tile_ids"),
+            _abi.ptr(gaussian_ids, I32, "gaussian_ids"), _abi.ptr(vals_out, I32, "gaussian_ids_sorted"),
+            _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(digit_hist, I32, "digit_hist"),
+            _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()), "sb_sort_tiles_global")
+        return num_intersects, None, vals_out, tile_bins, view_ends
+    keys_out = torch.empty_like(isect_ids)
     if num_intersects > 0:
-        emit = lib.sb_map_gaussian_to_tiles_ordered if compact else lib.sb_map_gaussian_to_intersects_ordered
-        _abi.check(emit(
+        _abi.check(lib.sb_map_gaussian_to_intersects_ordered(
             num_views, n, _abi.ptr(xys, F32, "xys"), xys_stride, _abi.ptr(depths, F32, "depths"),
             _abi.ptr(radii, I32, "radii"), _abi.ptr(order, I32, "order"), _abi.ptr(cum, I32, "cum_tiles_hit"),
             tiles_x, tiles_y, block_width, _abi.ptr(isect_ids, kdt, "isect_ids"),
             _abi.ptr(gaussian_ids, I32, "gaussian_ids"), _abi.stream()), "ordered key emission")
-        if compact:
-            tmp = _scratch(lib.sb_sort32_temp_bytes(num_intersects), dev)
-            _abi.check(lib.sb_sort_pairs32(num_intersects, tile_bits, _abi.ptr(isect_ids, kdt, "tile_ids"),
+        tmp = _scratch(lib.sb_sort_temp_bytes(num_intersects), dev)
+        _abi.check(lib.sb_sort_pairs_range(num_intersects, 32, 32 + tile_bits,
+                                           _abi.ptr(isect_ids, I64, "isect_ids"),
                                            _abi.ptr(gaussian_ids, I32, "gaussian_ids"),
-                                           _abi.ptr(keys_out, kdt, "tile_ids_sorted"),
+                                           _abi.ptr(keys_out, I64, "isect_ids_sorted"),
                                            _abi.ptr(vals_out, I32, "gaussian_ids_sorted"),
                                            _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()),
-                       "sb_sort_pairs32")
-        else:
-            tmp = _scratch(lib.sb_sort_temp_bytes(num_intersects), dev)
-            _abi.check(lib.sb_sort_pairs_range(num_intersects, 32, 32 + tile_bits,
-                                               _abi.ptr(isect_ids, I64, "isect_ids"),
-                                               _abi.ptr(gaussian_ids, I32, "gaussian_ids"),
-                                               _abi.ptr(keys_out, I64, "isect_ids_sorted"),
-                                               _abi.ptr(vals_out, I32, "gaussian_ids_sorted"),
-                                               _abi.ptr(tmp, torch.uint8, "temp"), tmp.numel(), _abi.stream()),
-                       "sb_sort_pairs_range")
+                   "sb_sort_pairs_range")
     del isect_ids, gaussian_ids
-    if compact:
-        tile_bins = torch.zeros(tiles_total, 2, dtype=I32, device=dev)
-        _abi.check(lib.sb_tile_bin_edges32(num_intersects, _abi.ptr(keys_out, kdt, "tile_ids_sorted"), tiles_total,
-                                           _abi.ptr(tile_bins, I32, "tile_bins"), _abi.stream()),
-                   "sb_tile_bin_edges32")
-    else:
-        tile_bins = get_tile_bin_edges(num_intersects, keys_out, tile_bounds, num_views)
-    # emission is view-major (the view is the top of the pre-order key): offsets at the view boundaries
-    view_ends = cum.view(num_views, n)[:, -1] if total > 0 else cum
+    tile_bins = get_tile_bin_edges(num_intersects, keys_out, tile_bounds, num_views)
     return num_intersects, keys_out, vals_out, tile_bins, view_ends

@@ -474,11 +474,17 @@ class _RenderViews(Function):
             ctx.opac_shape = opac_shape
             ctx.color_shapes = (tuple(color_src.shape), None if color_rest is None else tuple(color_rest.shape))
             ctx.set_materialize_grads(False)
+            # OUTPUTS must not hang off ctx as plain attributes: output -> grad_fn (= ctx) -> ps -> output is a
+            # reference cycle that only Python's cyclic collector breaks, and until it runs every step's buffers
+            # (> 1 GB) stay allocated.  save_for_backward handles outputs without the cycle.
+            out_img, out_alpha = ps.out_img, ps.out_alpha
+            ps.out_img = ps.out_alpha = None
+            ctx.save_for_backward(out_img, out_alpha)
             if gt is not None:
                 l1_sum, sq_sum = ps.loss_sums[:, 0], ps.loss_sums[:, 1]
                 ctx.mark_non_differentiable(sq_sum)
-                return l1_sum, sq_sum, ps.out_img
-            return ps.out_img, ps.out_alpha
+                return l1_sum, sq_sum, out_img
+            return out_img, out_alpha
 
     @staticmethod
     def backward(ctx, *grads):
@@ -495,6 +501,14 @@ class _RenderViews(Function):
             v_l1 = None
             if v_out_img is None and v_out_alpha is None:
                 return (None,) * nin
+        ps.out_img, ps.out_alpha = ctx.saved_tensors
+        try:
+            return _RenderViews._backward(ctx, ps, dev, nin, v_l1, v_out_img, v_out_alpha)
+        finally:
+            ps.out_img = ps.out_alpha = None
+
+    @staticmethod
+    def _backward(ctx, ps, dev, nin, v_l1, v_out_img, v_out_alpha):
         with torch.cuda.device(dev):
             lib, p = _abi.load(), _abi.ptr
             st = _abi.stream()

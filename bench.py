@@ -208,6 +208,168 @@ def cpu_baseline(views: int) -> dict:
             "seconds": dt}
 
 
+def run_config3(args, steps, rank, world, dev, timed, V, H, W, n):
+    """8 scenes x 32 views per step on `world` GPUs.
+    scene-sharded: rank r renders scenes r, r + G, ... (SplatFormer's DDP layout, no collective);
+    view-sharded : every scene's views are split over the ranks, Gaussians replicated; the per-Gaussian
+                   gradients of scene i are all-reduced (NCCL, in place on the backward's flat buffer) while
+                   scene i + 1 renders; the step ends when every reduce has landed."""
+    import torch.distributed as dist
+    from splatformer_b200 import dist as sbdist
+    from splatformer_b200 import gs_utils, render, synth
+    S = args.config3_scenes
+    inv_views = 1.0 / V
+    pix_step = S * V * H * W
+    out = {"workload": f"{S} scenes x {V} views of {n} Gaussians per step (BASELINE config 3)", "steps": steps,
+           "unit": UNIT}
+
+    def load(sid, lo, hi):
+        gs, cams, gt = synth.make_config(WORKLOAD, 100 + sid, num_views=V)
+        gt = (gt * 255.0).round().to(torch.uint8)
+        cams = dict(cams)
+        cams["camera_to_worlds"] = cams["camera_to_worlds"][lo:hi].contiguous()
+        return ({k: v.to(dev).requires_grad_() for k, v in gs.items()}, {k: v.to(dev) for k, v in cams.items()},
+                gt[lo:hi].contiguous().to(dev))
+
+    # ---- scene-sharded ----
+    mine = sbdist.scene_slice(S, rank, world)
+    scenes = [load(sid, 0, V) for sid in mine]
+    plan = render.RenderPlan()
+
+    def step_scene(i):
+        for raw, cams, gt in scenes:
+            for p in raw.values():
+                p.grad = None
+            l1, _ = gs_utils.render_l1_loss(raw, cams, gt, plan=plan)
+            (l1.sum() * inv_views).backward()
+
+    for i in range(2):
+        step_scene(i)
+    ms, _, _, _ = timed(step_scene, steps)
+    out["scene_sharded"] = {"value": pix_step / (ms / steps * 1e-3) / 1e6, "ms_per_step": ms / steps,
+                            "scenes_per_rank": len(mine), "collective": "none"}
+    del scenes
+    if world == 1:
+        out["view_sharded"] = None          # one GPU: the two layouts are the same loop
+        return out
+
+    # ---- view-sharded ----
+    lo, hi = sbdist.view_slice(V, rank, world)
+    scenes = [load(sid, lo, hi) for sid in range(S)]
+    plan_v = render.RenderPlan()
+
+    def step_view(sync, overlap):
+        def fn(i):
+            for raw, cams, gt in scenes:
+                for p in raw.values():
+                    p.grad = None
+                routed = sbdist.sync_gaussian_grads(raw, overlap=overlap) if sync else raw
+                l1, _ = gs_utils.render_l1_loss(routed, cams, gt, plan=plan_v)
+                (l1.sum() * inv_views).backward()
+            sbdist.wait_pending()
+        return fn
+
+    for i in range(2):
+        step_view(True, True)(i)
+    ms_ov, _, _, _ = timed(step_view(True, True), steps)
+    ms_blk, _, _, _ = timed(step_view(True, False), steps)
+    ms_none, _, _, _ = timed(step_view(False, False), steps)
+    # the exchange on its own: one all-reduce of a scene's flat gradient buffer
+    raw0 = scenes[0][0]
+    nfloat = sum(p.numel() for p in raw0.values())
+    buf = torch.zeros(nfloat, device=dev)
+    for _ in range(3):
+        dist.all_reduce(buf)
+
+    def ar(i):
+        dist.all_reduce(buf)
+    ms_ar, _, _, _ = timed(ar, 20)
+    ar_ms = ms_ar / 20
+    hidden = (ms_blk - ms_ov) / steps
+    out["view_sharded"] = {
+        "value": pix_step / (ms_ov / steps * 1e-3) / 1e6, "ms_per_step": ms_ov / steps,
+        "views_per_rank": hi - lo, "allreduces_per_step": S, "allreduce_bytes": nfloat * 4, "allreduce_ms": ar_ms,
+        "ms_per_step_blocking_allreduce": ms_blk / steps, "ms_per_step_without_allreduce": ms_none / steps,
+        "overlap_frac": max(0.0, min(1.0, 1.0 - (ms_ov - ms_none) / steps / max(S * ar_ms, 1e-9))),
+        "collective": "NCCL all-reduce(sum) of the flat (N, 11+3K) gradient buffer, in place, async under the next scene",
+        "nccl_ranks": dist.get_world_size(), "hidden_ms_per_step_vs_blocking": hidden,
+    }
+    # correctness on the device: the all-reduced gradients of scene 0 == the gradients of all its views on one GPU
+    raw, cams, gt = scenes[0]
+    for p in raw.values():
+        p.grad = None
+    routed = sbdist.sync_gaussian_grads(raw, overlap=False)
+    l1, _ = gs_utils.render_l1_loss(routed, cams, gt, plan=plan_v)
+    (l1.sum() * inv_views).backward()
+    full_raw, full_cams, full_gt = load(0, 0, V)
+    l1f, _ = gs_utils.render_l1_loss(full_raw, full_cams, full_gt)
+    (l1f.sum() * inv_views).backward()
+    worst = 0.0
+    for k in raw:
+        a, b = raw[k].grad.double(), full_raw[k].grad.double()
+        worst = max(worst, float((a - b).norm() / b.norm().clamp_min(1e-30)))
+    t = torch.tensor([worst], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out["view_sharded"]["grad_rel_l2_vs_single_gpu"] = float(t.item())
+    if float(t.item()) > 1e-4:
+        raise SystemExit(f"view-sharded gradients differ from the single-GPU ones: rel L2 {float(t.item()):.3e}")
+    return out
+
+
+def run_other_configs(dev):
+    """BASELINE configs 4 (1M Gaussians, 8 views 1080p, forward only) and 5 (6M Gaussians, 2 views 4K, fwd+bwd)."""
+    from splatformer_b200 import gs_utils, render, synth
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    res = []
+    for name, views, backward, steps in (("real_1m_sh3_1080p", 8, False, 5), ("stress_6m_4k", 2, True, 4)):
+        c = synth.CONFIGS[name]
+        gs, cams, gt = synth.make_config(name, 0, num_views=views)
+        gt = (gt * 255.0).round().to(torch.uint8).to(dev)
+        cams = {k: v.to(dev) for k, v in cams.items()}
+        raw = {k: v.to(dev).requires_grad_(backward) for k, v in gs.items()}
+        plan = render.RenderPlan()
+
+        def step():
+            if backward:
+                for p in raw.values():
+                    p.grad = None
+                l1, _ = gs_utils.render_l1_loss(raw, cams, gt, plan=plan)
+                (l1.sum() / views).backward()
+            else:
+                with torch.no_grad():
+                    gs_utils.render_scene(raw, **cams, plan=plan)
+
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            step()
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / steps
+        isect = render.last_num_intersects() / views
+        k = (c["deg"] + 1) ** 2
+        tiles = ((c["width"] + 15) // 16) * ((c["height"] + 15) // 16)
+        per_view = stage_bytes_per_view(c["n"], k, isect, c["height"] * c["width"], tiles)
+        fwd_keys = ("project_sh_fwd", "cumsum", "map_isect", "sort", "bin_edges", "raster_fwd")
+        b_alg = sum(v for kk, v in per_view.items() if backward or kk in fwd_keys) * views
+        res.append({"workload": name, "gaussians": c["n"], "views": views, "image": [c["height"], c["width"]],
+                    "pass": "fwd+bwd" if backward else "fwd", "steps": steps, "ms_per_step": ms,
+                    "mpix_per_s": views * c["height"] * c["width"] / (ms * 1e-3) / 1e6,
+                    "intersections_per_view": isect, "alg_bytes_per_step": b_alg,
+                    "hbm_frac": b_alg / (ms * 1e-3) / 1e9 / peak, "binning": "global sort (hand-written one-sweep radix)"})
+        del raw, gs, gt
+        torch.cuda.empty_cache()
+    return res
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -226,6 +388,11 @@ def main() -> None:
                     help="where the e2e loop enqueues the next scene's host->device upload")
     ap.add_argument("--wrapper-steps", type=int, default=5,
                     help="timed steps of the unmodified per-view wrapper path (0 = skip)")
+    ap.add_argument("--config3-steps", type=int, default=None,
+                    help="timed steps of the 8-scene train-step shape (default: steps // 5, at least 4; 0 = skip)")
+    ap.add_argument("--config3-scenes", type=int, default=8)
+    ap.add_argument("--other-configs", type=int, default=1,
+                    help="1: also time BASELINE configs 4 and 5 (single GPU) after the headline; 0: skip")
     ap.add_argument("--ref-views", type=int, default=2)
     ap.add_argument("--steps-ref", type=int, default=None)
     ap.add_argument("--warmup-ref", type=int, default=None)
@@ -417,6 +584,15 @@ def main() -> None:
         for i in range(2):
             step_wrapper(i)
         wrapper_ms, wrapper_launches, _, _ = timed(step_wrapper, args.wrapper_steps)
+    # ---- BASELINE config 3: the train-step render loss, 8 scenes x 32 views per step, in BOTH layouts ----
+    config3 = None
+    c3_steps = args.config3_steps if args.config3_steps is not None else max(4, args.steps // 5)
+    if c3_steps > 0:
+        config3 = run_config3(args, c3_steps, rank, world, dev, timed, V, H, W, n)
+    # ---- BASELINE configs 4 and 5 (one GPU): driver-visible numbers for the other named shapes ----
+    other = None
+    if args.other_configs and world == 1:
+        other = run_other_configs(dev)
     clocks = sampler.stop() if sampler else None
 
     if rank == 0:
@@ -484,6 +660,10 @@ def main() -> None:
                                   "region) + the binning totals (8 B, read when the backward starts)",
                            "api": "splatformer_b200.loader.ScenePrefetcher(" + ("loader.pack_scene(host scene)" if args.e2e_packed else "host scenes") + ") -> gs_utils.render_l1_loss(gs_params, "
                                   "cameras, images) + backward + pinned read of the loss"}
+        if config3 is not None:
+            line["config3"] = config3
+        if other is not None:
+            line["configs"] = other
         if wrapper_ms is not None:
             w_step = wrapper_ms / args.wrapper_steps
             line["wrapper_path"] = {"value": pix_step / (w_step * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": w_step,

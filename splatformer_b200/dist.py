@@ -8,6 +8,12 @@
   gradients.  They are packed into ONE (N, 11 + 3K) float32 buffer (means 3, scales 3, quats 4,
   opacity 1, SH 3K) and reduced with a single NCCL all-reduce over NVLink / NVSwitch.
 
+  `SyncGaussianGrads` puts that exchange INTO the autograd graph, between the scene's parameters and
+  the render: the render's backward writes all per-Gaussian gradients into one flat allocation
+  (render.grad_layout), so the all-reduce runs in place on exactly that buffer -- no pack, no unpack --
+  and, launched asynchronously, proceeds on NCCL's stream while the next scene renders on the compute
+  stream (`wait_pending()` joins them before the gradients are used).
+
 Works with any torch.distributed backend (the CPU tests run it on gloo with world_size 2).
 """
 from __future__ import annotations
@@ -76,3 +82,80 @@ def allreduce_gaussian_grads(params: Dict[str, Tensor], group=None, async_op: bo
         return work, (lambda: unpack_grads(buf, layout, params))
     unpack_grads(buf, layout, params)
     return None
+
+
+# ---------------------------------------------------------------------------------------------
+# The exchange inside the autograd graph
+# ---------------------------------------------------------------------------------------------
+_pending: list = []
+
+
+def wait_pending() -> int:
+    """Make the current stream wait for every all-reduce launched by SyncGaussianGrads(overlap=True) so far
+    (a stream-side wait for NCCL, a blocking one for gloo).  Returns how many were outstanding."""
+    n = len(_pending)
+    for work, keep in _pending:
+        work.wait()
+    _pending.clear()
+    return n
+
+
+def _as_one_buffer(grads: Sequence[Tensor]):
+    """If the gradients are disjoint contiguous blocks of ONE allocation (what render._RenderViews.backward
+    returns), the flat tensor spanning them; else None."""
+    if any(g is None or not g.is_contiguous() for g in grads):
+        return None
+    st = grads[0].untyped_storage()
+    if any(g.untyped_storage().data_ptr() != st.data_ptr() or g.dtype != grads[0].dtype for g in grads):
+        return None
+    spans = sorted((g.storage_offset(), g.storage_offset() + g.numel()) for g in grads)
+    for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+        if b0 < a1 or b0 - a1 > 3:            # overlap, or a hole larger than the 16-byte block alignment
+            return None
+    lo, hi = spans[0][0], spans[-1][1]
+    flat = grads[0].new_empty(0).set_(st, lo, (hi - lo,))
+    return flat
+
+
+class SyncGaussianGrads(torch.autograd.Function):
+    """y_i = x_i in the forward; in the backward the incoming gradients are summed over the ranks of `group`
+    with ONE all-reduce.  Usage (view-sharded scene): params = SyncGaussianGrads.apply(group, overlap, *params)
+    before handing them to the render.  overlap=True launches the all-reduce asynchronously and returns at
+    once; the gradients must then reach fresh `.grad` fields (no accumulation into an existing one) and
+    `wait_pending()` must be called before they are read."""
+
+    @staticmethod
+    def forward(ctx, group, overlap, *params):
+        ctx.group, ctx.overlap = group, bool(overlap)
+        return tuple(p.view_as(p) for p in params)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        world = dist.get_world_size(ctx.group) if (dist.is_available() and dist.is_initialized()) else 1
+        live = [g for g in grads if g is not None]
+        if world > 1 and live:
+            flat = _as_one_buffer(live)
+            packed = None
+            if flat is None:                   # generic fallback: gather the pieces, reduce, scatter back
+                packed = torch.cat([g.reshape(-1).to(torch.float32) for g in live])
+                flat = packed
+            work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=ctx.group, async_op=True)
+            if packed is None and ctx.overlap:
+                _pending.append((work, flat))
+            else:
+                work.wait()
+                if packed is not None:
+                    off = 0
+                    for g in live:
+                        g.copy_(packed[off:off + g.numel()].view_as(g))
+                        off += g.numel()
+        return (None, None) + tuple(grads)
+
+
+def sync_gaussian_grads(params: Dict[str, Tensor], group=None, overlap: bool = False) -> Dict[str, Tensor]:
+    """The per-Gaussian tensors of `params` routed through SyncGaussianGrads (others passed through)."""
+    keys = [k for k in GRAD_KEYS if k in params and params[k].requires_grad]
+    outs = SyncGaussianGrads.apply(group, overlap, *[params[k] for k in keys])
+    res = dict(params)
+    res.update(dict(zip(keys, outs)))
+    return res

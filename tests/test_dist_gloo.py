@@ -96,3 +96,67 @@ def test_view_sharded_gradients_sum_to_whole_scene(tmp_path):
     for k in raw:
         assert torch.equal(r0["grads"][k], r1["grads"][k]), "ranks disagree after the all-reduce"
         assert torch.allclose(r0["grads"][k], raw[k].grad, rtol=1e-4, atol=1e-7), k
+
+
+def _sync_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from splatformer_b200 import render
+        torch.manual_seed(rank)
+        n, k = 40, 4
+        params = {"means": torch.randn(n, 3), "scales": torch.randn(n, 3), "quats": torch.randn(n, 4),
+                  "opacities": torch.randn(n, 1), "features_dc": torch.randn(n, 3),
+                  "features_rest": torch.randn(n, k - 1, 3)}
+        params = {kk: v.requires_grad_() for kk, v in params.items()}
+
+        class FlatGrads(torch.autograd.Function):
+            """Stands in for the render: its backward hands out blocks of ONE flat buffer (render.grad_layout)."""
+            @staticmethod
+            def forward(ctx, *xs):
+                ctx.shapes = [tuple(x.shape) for x in xs]
+                return sum((x * (i + 1)).sum() for i, x in enumerate(xs))
+
+            @staticmethod
+            def backward(ctx, g):
+                blocks, size = render.grad_layout(n, ctx.shapes[4], ctx.shapes[5])
+                flat = torch.empty(size)
+                outs = []
+                for i, (name, off, shape) in enumerate(blocks):
+                    cnt = 1
+                    for d in shape:
+                        cnt *= d
+                    view = flat[off:off + cnt].view(shape)
+                    view.fill_(float(i + 1) * (rank + 1))
+                    outs.append(view)
+                FlatGrads.flat = flat
+                return tuple(outs)
+
+        for overlap in (False, True):
+            for p in params.values():
+                p.grad = None
+            routed = sbdist.sync_gaussian_grads(params, overlap=overlap)
+            keys = ("means", "scales", "quats", "opacities", "features_dc", "features_rest")
+            FlatGrads.apply(*[routed[kk] for kk in keys]).backward()
+            assert sbdist.wait_pending() == (1 if overlap else 0)
+            for i, kk in enumerate(keys):
+                want = float(i + 1) * sum(r + 1 for r in range(world))
+                assert torch.all(params[kk].grad == want), (kk, overlap)
+                # in place on the render's buffer: the leaf gradient is a block of it, nothing was packed
+                assert params[kk].grad.untyped_storage().data_ptr() == FlatGrads.flat.untyped_storage().data_ptr()
+        # generic fallback: gradients that are separate allocations
+        for p in params.values():
+            p.grad = None
+        routed = sbdist.sync_gaussian_grads(params)
+        sum((routed[kk] * (rank + 2)).sum() for kk in params).backward()
+        for kk in params:
+            assert torch.all(params[kk].grad == float(sum(r + 2 for r in range(world)))), kk
+        torch.save({"ok": True}, os.path.join(out_dir, f"sync{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sync_gaussian_grads_reduces_in_place_on_the_flat_buffer(tmp_path):
+    world = 2
+    mp.spawn(_sync_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert all(os.path.exists(os.path.join(tmp_path, f"sync{r}.pt")) for r in range(world))

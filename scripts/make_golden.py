@@ -8,7 +8,9 @@ tests/test_oracle_known_answers.py and tests/test_oracle_crosscheck.py -- are wh
 
 Each file holds the raw SplatFormer-style inputs, the cameras, and per view: the projection
 outputs, intersection count, sorted ids, tile bins, rendered rgb / alpha, the per-pixel decision
-margin, plus the gradients of sum_v mean(|rgb_v - gt_v| * solid_v) w.r.t. the raw parameters."""
+margin, plus the gradients of sum_v mean(|rgb_v - gt_v| * solid_v) w.r.t. the raw parameters -- from the
+float32 oracle (grad_*, what the CPU test re-derives) and from the FLOAT64 oracle with the same pixel mask
+(grad64_*, the reference of the GPU test's 1e-3 tolerance)."""
 import os
 import sys
 
@@ -64,6 +66,16 @@ def make(name):
     out["loss"] = np.float64(loss.detach())
     for k in gs:
         out[f"grad_{k}"] = raw[k].grad.numpy()
+    raw64 = {k: v.double().requires_grad_() for k, v in gs.items()}
+    loss64 = 0.0
+    for v in range(views):
+        rgb64, _ = R.render_view(raw64, cams["camera_to_worlds"][v].double(), cx, cy, fx, fy, w, h,
+                                 cams["background_color"])
+        solid = torch.from_numpy(out[f"v{v}_solid"])
+        loss64 = loss64 + ((rgb64 - gt[v].double()).abs() * solid[..., None]).mean()
+    loss64.backward()
+    for k in gs:
+        out[f"grad64_{k}"] = raw64[k].grad.numpy()
     path = os.path.join(ROOT, "tests", "golden", name + ".npz")
     np.savez_compressed(path, **out)
     print(name, os.path.getsize(path) // 1024, "KiB", "loss", float(loss))

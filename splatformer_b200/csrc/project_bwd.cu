@@ -126,11 +126,12 @@ __device__ __forceinline__ float max_view_lanes(float x) {
 }
 
 // shared memory: [rows][padded row] staging of the SH gradients | [3K][block] per-thread SH sums | counts | lists
-__host__ __device__ inline size_t views_bwd_smem_bytes(int k3_store, bool sh) {
+__host__ __device__ inline size_t views_bwd_smem_bytes(int k3_store, bool sh, int num_views) {
   const size_t stage = sh ? (size_t)kViewsBwdRows * (k3_store | 1) * sizeof(float) : 0;
   const size_t priv = sh ? (size_t)k3_store * kViewsBwdBlock * sizeof(float) : 0;
   const size_t lists = (size_t)kViewsBwdRows * kBwdViewChunk + (size_t)kViewsBwdRows * sizeof(int);
-  return stage + priv + ((lists + 15) & ~(size_t)15);
+  const size_t cams = num_views <= kMaxStagedCams ? (size_t)num_views * kCamFloats * sizeof(float) : 0;
+  return stage + priv + ((lists + 15) & ~(size_t)15) + cams;
 }
 
 template <int DEG>
@@ -153,6 +154,15 @@ __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_projec
   const int k3u = DEG >= 0 ? KU * 3 : 0;
   int* s_cnt = reinterpret_cast<int*>(smem + kViewsBwdRows * row_stride + (DEG >= 0 ? k3_store * kViewsBwdBlock : 0));   // [rows]
   unsigned char* s_list = reinterpret_cast<unsigned char*>(s_cnt + kViewsBwdRows);         // [rows][kBwdViewChunk]
+  // cameras: built once per block when there are few enough views
+  const bool cams_staged = num_views <= kMaxStagedCams;
+  float* s_cams = reinterpret_cast<float*>(
+      reinterpret_cast<unsigned char*>(s_cnt) +
+      (((size_t)kViewsBwdRows * kBwdViewChunk + kViewsBwdRows * sizeof(int) + 15) & ~(size_t)15));
+  if (cams_staged) {
+    stage_cams(cams, campos, num_views, img_w, img_h, s_cams);
+    __syncthreads();
+  }
   const int g0 = blockIdx.x * kViewsBwdRows;
   const int nb = min(kViewsBwdRows, n - g0);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -172,7 +182,16 @@ __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_projec
     float q[4] = {q4.x, q4.y, q4.z, q4.w};
     float qraw = 1.0f;
     if (flags & kFlagRawQuats) qraw = wrapper_normalise_quat(q);      // gs_utils.py:46-51
-    float am[3] = {0, 0, 0}, as[3] = {0, 0, 0}, aq[4] = {0, 0, 0, 0}, aop = 0.f;
+    // Sigma is view-independent; so is the chain Sigma -> (scale, quat), which is linear in dL/dSigma: the
+    // views' dL/dSigma are summed (six entries) and the chain runs once per Gaussian after the loop
+    float sg[6];
+    {
+      GaussCov gc;
+      gaussian_cov3d(s, glob, q, gc);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) sg[i] = gc.sg[i];
+    }
+    float am[3] = {0, 0, 0}, ag[6] = {0, 0, 0, 0, 0, 0}, aop = 0.f;
     float op = 0.f, col0 = 0.f, col1 = 0.f, col2 = 0.f;
 
     const int row0 = warp * kBwdRowsPerWarp;                       // scan phase: the warp's first Gaussian
@@ -210,30 +229,37 @@ __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_projec
       const unsigned char* my_list = s_list + rowi * kBwdViewChunk;
       for (int k = sub; k < my_cnt; k += kViewLanesB) {
         const int v = vc0 + my_list[k];
-        const Cam cam = load_cam(cams, v);
+        Cam cam;
+        float lim_x, lim_y;
+        if (cams_staged) {
+          cam = cam_from_smem(s_cams + v * kCamFloats, lim_x, lim_y);
+        } else {
+          cam = load_cam(cams, v);
+          cam_limits(cam, img_w, img_h, lim_x, lim_y);
+        }
         ProjFwd f;
-        project_fwd_one(m, s, glob, q, cam, img_w, img_h, bw, clip, f);
+        project_fwd_view(m, sg, cam, lim_x, lim_y, img_w, img_h, bw, clip, f);
         if (!f.valid) continue;                        // (a culled pair's record is never written: not reached)
         const size_t i = (size_t)v * n + gl;
         const float4 ga = __ldg(v_packed + 3 * i), gb = __ldg(v_packed + 3 * i + 1);
         const float gcx = __ldg(reinterpret_cast<const float*>(v_packed + 3 * i + 2));
         const float4 col = __ldg(packed + 3 * i + 2);       // r, g, b (after the clamp), opacity
         op = col.w; col0 = col.x; col1 = col.y; col2 = col.z;
-        float vm[3], vs[3], vq[4];
+        float vm[3], G[9];
         float vx, vy, vca, vcb, vcc, vop;
         moments_to_grads(ga, gb, f.ca, f.cb, f.cc, op, vx, vy, vca, vcb, vcc, vop);
-        project_bwd_one(m, s, glob, cam, f, vx, vy, 0.f, vca, vcb, vcc, 0.f, nullptr, vm, vs, vq, nullptr);
+        project_bwd_view(m, sg, cam, f, vx, vy, 0.f, vca, vcb, vcc, 0.f, vm, G, nullptr);
 #pragma unroll
-        for (int j = 0; j < 3; ++j) { am[j] += vm[j]; as[j] += vs[j]; }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) aq[j] += vq[j];
+        for (int j = 0; j < 3; ++j) am[j] += vm[j];
+        ag[0] += G[0]; ag[1] += G[1]; ag[2] += G[2]; ag[3] += G[4]; ag[4] += G[5]; ag[5] += G[8];
         aop += vop;
         float vr = gb.z, vg = gb.w, vb = gcx;
         if (DEG >= 0) {
           // clamp(x + 0.5, min 0): gradient passes where > 0
           vr = col.x > 0.f ? vr : 0.f; vg = col.y > 0.f ? vg : 0.f; vb = col.z > 0.f ? vb : 0.f;
           float Y[KU], cp[3];
-          load_campos(cams, campos, v, cp);
+          if (cams_staged) { const float* d = s_cams + v * kCamFloats; cp[0] = d[18]; cp[1] = d[19]; cp[2] = d[20]; }
+          else load_campos(cams, campos, v, cp);
           sh_basis(DEG, m[0] - cp[0], m[1] - cp[1], m[2] - cp[2], Y);
 #pragma unroll
           for (int j = 0; j < KU; ++j) {
@@ -254,10 +280,18 @@ __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_projec
     }
     // join the four view lanes of the Gaussian (op / colour are view-independent: take any lane that saw them)
 #pragma unroll
-    for (int k = 0; k < 3; ++k) { am[k] = sum_view_lanes(am[k]); as[k] = sum_view_lanes(as[k]); }
+    for (int k = 0; k < 3; ++k) am[k] = sum_view_lanes(am[k]);
 #pragma unroll
-    for (int k = 0; k < 4; ++k) aq[k] = sum_view_lanes(aq[k]);
+    for (int k = 0; k < 6; ++k) ag[k] = sum_view_lanes(ag[k]);
     aop = sum_view_lanes(aop);
+    // Sigma -> (scale, quat), once, from the summed dL/dSigma
+    float as[3], aq[4];
+    {
+      GaussCov gc;
+      gaussian_cov3d(s, glob, q, gc);
+      const float G[9] = {ag[0], ag[1], ag[2], ag[1], ag[3], ag[4], ag[2], ag[4], ag[5]};
+      cov3d_chain_bwd(s, glob, gc.M, gc.R, gc.qn, gc.qnorm, G, as, aq);
+    }
     if (DEG < 0) { acc[0] = sum_view_lanes(acc[0]); acc[1] = sum_view_lanes(acc[1]); acc[2] = sum_view_lanes(acc[2]); }
     op = max_view_lanes(op);
     if (DEG < 0 && (flags & kFlagColorSigmoid)) {
@@ -353,7 +387,7 @@ extern "C" int sb_views_project_bwd(int num_views, int n, const float* means, co
   sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0,
                   (flags & sb::kFlagIntrinsShared) ? 1 : 0};
   const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
-  const size_t smem = sb::views_bwd_smem_bytes(k3, sh_degree >= 0);
+  const size_t smem = sb::views_bwd_smem_bytes(k3, sh_degree >= 0, num_views);
   dim3 grid(sb::ceil_div(n, sb::kViewsBwdRows));
   cudaStream_t st = (cudaStream_t)stream;
   const float4* pk = reinterpret_cast<const float4*>(packed);

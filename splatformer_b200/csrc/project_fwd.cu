@@ -56,11 +56,10 @@ constexpr int kViewsBlock = 128;
 constexpr int kViewLanes = 4;                          // threads that share one Gaussian, each taking V/4 views
 constexpr int kViewsRows = kViewsBlock / kViewLanes;   // Gaussians per block
 
-#ifdef SB_PROJ_FWD_MINB
-#define SB_PROJ_FWD_BOUNDS __launch_bounds__(kViewsBlock, SB_PROJ_FWD_MINB)
-#else
-#define SB_PROJ_FWD_BOUNDS __launch_bounds__(kViewsBlock)
+#ifndef SB_PROJ_FWD_MINB
+#define SB_PROJ_FWD_MINB 4        // 128 registers: 0.211 ms vs 0.219 ms unbounded (156 registers) at the benchmark shape
 #endif
+#define SB_PROJ_FWD_BOUNDS __launch_bounds__(kViewsBlock, SB_PROJ_FWD_MINB)
 template <int DEG>
 __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
     int num_views, int n, const float* __restrict__ means, const float* __restrict__ scales, float glob,
@@ -86,6 +85,13 @@ __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
     }
     __syncthreads();
   }
+  // cameras: built once per block (shared memory after the SH staging rows) when there are few enough views
+  const bool cams_staged = num_views <= kMaxStagedCams;
+  float* s_cams = smem + (DEG >= 0 ? kViewsRows * padded_row(k3_store) : 0);
+  if (cams_staged) {
+    stage_cams(cams, campos, num_views, img_w, img_h, s_cams);
+    __syncthreads();
+  }
   const int g = g0 + rowi;
   if (rowi >= nb) return;
   if (DEG >= 0) {
@@ -104,14 +110,29 @@ __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
   if (flags & kFlagRawQuats) wrapper_normalise_quat(q);      // gs_utils.py:46-51
   float op = __ldg(opacities + g);
   if (flags & kFlagRawOpacities) op = sigmoidf_(op);
+  // Sigma = (R S)(R S)^T does not depend on the view: once per Gaussian, only its six entries stay live
+  float sg[6];
+  {
+    GaussCov gc;
+    gaussian_cov3d(s, glob, q, gc);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) sg[i] = gc.sg[i];
+  }
   // blocks start at different views so that, at any moment, the per-tile count reductions of the
   // resident blocks spread over all V*T counters instead of the T counters of one view
   const int v0 = blockIdx.x % num_views;
   for (int vi = sub; vi < num_views; vi += kViewLanes) {
     const int v = vi + v0 < num_views ? vi + v0 : vi + v0 - num_views;
-    const Cam cam = load_cam(cams, v);
+    Cam cam;
+    float lim_x, lim_y;
+    if (cams_staged) {
+      cam = cam_from_smem(s_cams + v * kCamFloats, lim_x, lim_y);
+    } else {
+      cam = load_cam(cams, v);
+      cam_limits(cam, img_w, img_h, lim_x, lim_y);
+    }
     ProjFwd o;
-    project_fwd_one(m, s, glob, q, cam, img_w, img_h, bw, clip, o);
+    project_fwd_view(m, sg, cam, lim_x, lim_y, img_w, img_h, bw, clip, o);
     const size_t i = (size_t)v * n + g;
     radii[i] = o.radius;
     tiles[i] = o.tiles;
@@ -167,7 +188,8 @@ __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
     float r, gg, b;
     if (DEG >= 0) {
       float Y[KU], cp[3];
-      load_campos(cams, campos, v, cp);
+      if (cams_staged) { const float* d = s_cams + v * kCamFloats; cp[0] = d[18]; cp[1] = d[19]; cp[2] = d[20]; }
+      else load_campos(cams, campos, v, cp);
       sh_basis(DEG, m[0] - cp[0], m[1] - cp[1], m[2] - cp[2], Y);
       r = 0.f; gg = 0.f; b = 0.f;
 #pragma unroll
@@ -224,7 +246,8 @@ extern "C" int sb_views_project_fwd(int num_views, int n, const float* means, co
   sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0,
                   (flags & sb::kFlagIntrinsShared) ? 1 : 0};
   const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
-  const size_t smem = sh_degree < 0 ? 0 : (size_t)sb::kViewsRows * (k3 | 1) * sizeof(float);
+  const size_t smem = (sh_degree < 0 ? 0 : (size_t)sb::kViewsRows * (k3 | 1) * sizeof(float)) +
+                      (num_views <= sb::kMaxStagedCams ? (size_t)num_views * sb::kCamFloats * sizeof(float) : 0);
   dim3 grid(sb::ceil_div(n, sb::kViewsRows));
   cudaStream_t st = (cudaStream_t)stream;
   float4* pk = reinterpret_cast<float4*>(packed);

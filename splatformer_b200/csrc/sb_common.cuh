@@ -50,6 +50,41 @@ __device__ __forceinline__ Cam load_cam(const CamSrc& s, int v) {
   return c;
 }
 
+// All views' cameras, built once per block into shared memory (world->camera matrix incl. the c2w inversion,
+// intrinsics, EWA clamp limits, camera centre: kCamFloats floats per view) instead of once per (view, Gaussian)
+// pair.  Needs a __syncthreads() before use.
+constexpr int kCamFloats = 24;     // w[9] p[3] fx fy cx cy | lim_x lim_y | centre[3] | pad
+constexpr int kMaxStagedCams = 64;
+
+__device__ __forceinline__ void stage_cams(const CamSrc& s, const float* __restrict__ campos, int num_views,
+                                           int img_w, int img_h, float* __restrict__ smem_cams) {
+  for (int v = threadIdx.x; v < num_views; v += blockDim.x) {
+    const Cam c = load_cam(s, v);
+    float* d = smem_cams + v * kCamFloats;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) d[i] = c.w[i];
+    d[9] = c.p[0]; d[10] = c.p[1]; d[11] = c.p[2];
+    d[12] = c.fx; d[13] = c.fy; d[14] = c.cx; d[15] = c.cy;
+    float lx, ly;
+    cam_limits(c, img_w, img_h, lx, ly);
+    d[16] = lx; d[17] = ly;
+    const float* m = s.viewmats + (size_t)v * s.stride;
+    if (s.c2w_opengl) { d[18] = __ldg(m + 3); d[19] = __ldg(m + 7); d[20] = __ldg(m + 11); }
+    else if (campos) { d[18] = __ldg(campos + 3 * v); d[19] = __ldg(campos + 3 * v + 1); d[20] = __ldg(campos + 3 * v + 2); }
+    else { d[18] = d[19] = d[20] = 0.f; }
+  }
+}
+
+__device__ __forceinline__ Cam cam_from_smem(const float* __restrict__ d, float& lim_x, float& lim_y) {
+  Cam c;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) c.w[i] = d[i];
+  c.p[0] = d[9]; c.p[1] = d[10]; c.p[2] = d[11];
+  c.fx = d[12]; c.fy = d[13]; c.cx = d[14]; c.cy = d[15];
+  lim_x = d[16]; lim_y = d[17];
+  return c;
+}
+
 // Camera centre of view v (for the SH view direction, gs_utils.py:67-69).
 __device__ __forceinline__ void load_campos(const CamSrc& s, const float* __restrict__ campos, int v, float* out) {
   if (s.c2w_opengl) {

@@ -107,7 +107,14 @@ SB_HD int sb_trunc_clamp(float v, int hi) {
 SB_HD void tile_bbox(float px, float py, float radius, int tiles_x, int tiles_y, int bw,
                      int& min_x, int& max_x, int& min_y, int& max_y) {
   const float fbw = (float)bw;
-  const float tcx = px / fbw, tcy = py / fbw, tr = radius / fbw;
+  float tcx, tcy, tr;
+  if ((bw & (bw - 1)) == 0) {
+    // a power of two: multiplying by the (exact) reciprocal gives the bits of the division
+    const float ibw = 1.0f / fbw;
+    tcx = px * ibw; tcy = py * ibw; tr = radius * ibw;
+  } else {
+    tcx = px / fbw; tcy = py / fbw; tr = radius / fbw;
+  }
   min_x = sb_trunc_clamp(tcx - tr, tiles_x);
   max_x = sb_trunc_clamp(tcx + tr + 1.0f, tiles_x);
   min_y = sb_trunc_clamp(tcy - tr, tiles_y);
@@ -130,11 +137,42 @@ SB_HD float wrapper_normalise_quat(float* q) {
   return n;
 }
 
-SB_HD void project_fwd_one(const float* m, const float* s, float glob, const float* q,
-                           const Cam& cam, int img_w, int img_h, int bw, float clip, ProjFwd& o) {
+// View-independent half of the projection: quaternion normalisation, rotation, M = R diag(glob * s),
+// Sigma = M M^T.  One call per Gaussian; the fused multi-view kernels keep only `sg` across their view loop.
+struct GaussCov {
+  float sg[6];                    // Sigma: s00 s01 s02 s11 s12 s22  (= the cov3d output)
+  float M[9], R[9], qn[4], qnorm;
+};
+
+SB_HD void gaussian_cov3d(const float* s, float glob, const float* q, GaussCov& c) {
+  const float qn = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  const float qw = q[0] / qn, qx = q[1] / qn, qy = q[2] / qn, qz = q[3] / qn;
+  c.qnorm = qn; c.qn[0] = qw; c.qn[1] = qx; c.qn[2] = qy; c.qn[3] = qz;
+  float* R = c.R;
+  R[0] = 1.0f - 2.0f * (qy * qy + qz * qz); R[1] = 2.0f * (qx * qy - qw * qz); R[2] = 2.0f * (qx * qz + qw * qy);
+  R[3] = 2.0f * (qx * qy + qw * qz); R[4] = 1.0f - 2.0f * (qx * qx + qz * qz); R[5] = 2.0f * (qy * qz - qw * qx);
+  R[6] = 2.0f * (qx * qz - qw * qy); R[7] = 2.0f * (qy * qz + qw * qx); R[8] = 1.0f - 2.0f * (qx * qx + qy * qy);
+  const float s0 = glob * s[0], s1 = glob * s[1], s2 = glob * s[2];
+  float* M = c.M;
+  for (int i = 0; i < 3; ++i) { M[3 * i] = R[3 * i] * s0; M[3 * i + 1] = R[3 * i + 1] * s1; M[3 * i + 2] = R[3 * i + 2] * s2; }
+#define SB_SIG(i, j) (M[3 * (i)] * M[3 * (j)] + M[3 * (i) + 1] * M[3 * (j) + 1] + M[3 * (i) + 2] * M[3 * (j) + 2])
+  c.sg[0] = SB_SIG(0, 0); c.sg[1] = SB_SIG(0, 1); c.sg[2] = SB_SIG(0, 2);
+  c.sg[3] = SB_SIG(1, 1); c.sg[4] = SB_SIG(1, 2); c.sg[5] = SB_SIG(2, 2);
+#undef SB_SIG
+}
+
+// 1.3 * tan(fov / 2) limits of the EWA clamp (A.2): a property of the camera, not of the Gaussian.
+SB_HD void cam_limits(const Cam& cam, int img_w, int img_h, float& lim_x, float& lim_y) {
+  lim_x = 1.3f * ((0.5f * (float)img_w) / cam.fx);
+  lim_y = 1.3f * ((0.5f * (float)img_h) / cam.fy);
+}
+
+// View-dependent half, given Sigma.  Does not touch o.cov3d / o.M / o.R / o.qn / o.qnorm.
+// inv_bw: 1 / bw when that is exact (bw a power of two), else 0 (then the tile bbox divides by bw).
+SB_HD void project_fwd_view(const float* m, const float* sg6, const Cam& cam, float lim_x, float lim_y,
+                            int img_w, int img_h, int bw, float clip, ProjFwd& o) {
   o.valid = false; o.front = false; o.radius = 0; o.tiles = 0;
   o.px = o.py = o.depth = o.ca = o.cb = o.cc = o.comp = 0.0f;
-  for (int i = 0; i < 6; ++i) o.cov3d[i] = 0.0f;
   const float* w = cam.w;
   const float x = m[0], y = m[1], z = m[2];
   const float tx = w[0] * x + w[1] * y + w[2] * z + cam.p[0];
@@ -143,26 +181,9 @@ SB_HD void project_fwd_one(const float* m, const float* s, float glob, const flo
   o.tx = tx; o.ty = ty; o.tz = tz;
   if (!(tz > clip)) return;
   o.front = true;
-
-  const float qn = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
-  const float qw = q[0] / qn, qx = q[1] / qn, qy = q[2] / qn, qz = q[3] / qn;
-  o.qnorm = qn; o.qn[0] = qw; o.qn[1] = qx; o.qn[2] = qy; o.qn[3] = qz;
-  float* R = o.R;
-  R[0] = 1.0f - 2.0f * (qy * qy + qz * qz); R[1] = 2.0f * (qx * qy - qw * qz); R[2] = 2.0f * (qx * qz + qw * qy);
-  R[3] = 2.0f * (qx * qy + qw * qz); R[4] = 1.0f - 2.0f * (qx * qx + qz * qz); R[5] = 2.0f * (qy * qz - qw * qx);
-  R[6] = 2.0f * (qx * qz - qw * qy); R[7] = 2.0f * (qy * qz + qw * qx); R[8] = 1.0f - 2.0f * (qx * qx + qy * qy);
-  const float s0 = glob * s[0], s1 = glob * s[1], s2 = glob * s[2];
-  float* M = o.M;
-  for (int i = 0; i < 3; ++i) { M[3 * i] = R[3 * i] * s0; M[3 * i + 1] = R[3 * i + 1] * s1; M[3 * i + 2] = R[3 * i + 2] * s2; }
-#define SB_SIG(i, j) (M[3 * (i)] * M[3 * (j)] + M[3 * (i) + 1] * M[3 * (j) + 1] + M[3 * (i) + 2] * M[3 * (j) + 2])
-  const float s00 = SB_SIG(0, 0), s01 = SB_SIG(0, 1), s02 = SB_SIG(0, 2);
-  const float s11 = SB_SIG(1, 1), s12 = SB_SIG(1, 2), s22 = SB_SIG(2, 2);
-#undef SB_SIG
-  o.cov3d[0] = s00; o.cov3d[1] = s01; o.cov3d[2] = s02; o.cov3d[3] = s11; o.cov3d[4] = s12; o.cov3d[5] = s22;
+  const float s00 = sg6[0], s01 = sg6[1], s02 = sg6[2], s11 = sg6[3], s12 = sg6[4], s22 = sg6[5];
   const float sg[9] = {s00, s01, s02, s01, s11, s12, s02, s12, s22};
 
-  const float lim_x = 1.3f * ((0.5f * (float)img_w) / cam.fx);
-  const float lim_y = 1.3f * ((0.5f * (float)img_h) / cam.fy);
   const float rz = 1.0f / tz;
   const float rz2 = rz * rz;
   const float ux = tx * rz, uy = ty * rz;
@@ -215,15 +236,37 @@ SB_HD void project_fwd_one(const float* m, const float* s, float glob, const flo
   o.radius = (int)radius; o.tiles = area;
 }
 
+SB_HD void project_fwd_one(const float* m, const float* s, float glob, const float* q,
+                           const Cam& cam, int img_w, int img_h, int bw, float clip, ProjFwd& o) {
+  for (int i = 0; i < 6; ++i) o.cov3d[i] = 0.0f;
+  // the near-plane test comes first in A.2: cov3d is only an output for Gaussians in front of it
+  const float tz = cam.w[6] * m[0] + cam.w[7] * m[1] + cam.w[8] * m[2] + cam.p[2];
+  GaussCov gc;
+  float lim_x, lim_y;
+  cam_limits(cam, img_w, img_h, lim_x, lim_y);
+  if (tz > clip) {
+    gaussian_cov3d(s, glob, q, gc);
+    for (int i = 0; i < 6; ++i) o.cov3d[i] = gc.sg[i];
+    for (int i = 0; i < 9; ++i) { o.M[i] = gc.M[i]; o.R[i] = gc.R[i]; }
+    for (int i = 0; i < 4; ++i) o.qn[i] = gc.qn[i];
+    o.qnorm = gc.qnorm;
+  } else {
+    for (int i = 0; i < 6; ++i) gc.sg[i] = 0.0f;
+  }
+  project_fwd_view(m, gc.sg, cam, lim_x, lim_y, img_w, img_h, bw, clip, o);
+}
+
 // ------------------------------------------------------------------------------------------
 // A.7 projection backward (VJP of project_fwd_one for a Gaussian with valid == true, given
 // the forward record `f`).  v_cov3d may be nullptr.  Outputs are *assigned*.
 // v_vm (12 floats: d/d viewmat[:3,:4] row-major) is accumulated into if non-null.
 // ------------------------------------------------------------------------------------------
-SB_HD void project_bwd_one(const float* m, const float* s, float glob, const Cam& cam,
-                           const ProjFwd& f, float v_px, float v_py, float v_depth, float v_k0,
-                           float v_k1, float v_k2, float v_comp, const float* v_cov3d,
-                           float* v_mean, float* v_scale, float* v_quat, float* v_vm) {
+// Part A, per (view, Gaussian): everything up to the gradient of Sigma.  Inputs are the forward record `f`
+// of project_fwd_view and Sigma; outputs v_mean (assigned) and the symmetric 3x3 gradient G = dL/dSigma
+// (assigned; its six distinct entries appear twice).  v_vm as in project_bwd_one.
+SB_HD void project_bwd_view(const float* m, const float* sg6, const Cam& cam, const ProjFwd& f, float v_px,
+                            float v_py, float v_depth, float v_k0, float v_k1, float v_k2, float v_comp,
+                            float* v_mean, float* G, float* v_vm) {
   const float* w = cam.w;
   const float a = f.a, b = f.b, c = f.c, det = f.det;
   const float inv_det2 = 1.0f / (det * det);
@@ -242,11 +285,7 @@ SB_HD void project_bwd_one(const float* m, const float* s, float glob, const Cam
   }
   // cov2d = T Sigma T^T ; symmetric gradient V2 = [[v_a, v_b/2],[v_b/2, v_c]]
   const float* T0 = f.T0; const float* T1 = f.T1;
-  const float* M = f.M;
-  float sg[9];
-  for (int i = 0; i < 3; ++i)
-    for (int j = 0; j < 3; ++j)
-      sg[3 * i + j] = M[3 * i] * M[3 * j] + M[3 * i + 1] * M[3 * j + 1] + M[3 * i + 2] * M[3 * j + 2];
+  const float sg[9] = {sg6[0], sg6[1], sg6[2], sg6[1], sg6[3], sg6[4], sg6[2], sg6[4], sg6[5]};
   float st0[3], st1[3];  // Sigma * T0, Sigma * T1
   for (int i = 0; i < 3; ++i) {
     st0[i] = sg[3 * i] * T0[0] + sg[3 * i + 1] * T0[1] + sg[3 * i + 2] * T0[2];
@@ -257,18 +296,11 @@ SB_HD void project_bwd_one(const float* m, const float* s, float glob, const Cam
     v_T0[i] = 2.0f * v_a * st0[i] + v_b * st1[i];
     v_T1[i] = v_b * st0[i] + 2.0f * v_c * st1[i];
   }
-  // G3 = T^T V2 T (symmetric 3x3) + direct cov3d gradient
-  float G[9];
+  // G = T^T V2 T (symmetric 3x3)
   const float hb = 0.5f * v_b;
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j)
       G[3 * i + j] = v_a * T0[i] * T0[j] + hb * (T0[i] * T1[j] + T1[i] * T0[j]) + v_c * T1[i] * T1[j];
-  if (v_cov3d) {
-    G[0] += v_cov3d[0]; G[4] += v_cov3d[3]; G[8] += v_cov3d[5];
-    G[1] += 0.5f * v_cov3d[1]; G[3] += 0.5f * v_cov3d[1];
-    G[2] += 0.5f * v_cov3d[2]; G[6] += 0.5f * v_cov3d[2];
-    G[5] += 0.5f * v_cov3d[4]; G[7] += 0.5f * v_cov3d[4];
-  }
   // J chain
   const float tz = f.tz, rz = 1.0f / tz, rz2 = rz * rz;
   float v_j00 = 0.f, v_j02 = 0.f, v_j11 = 0.f, v_j12 = 0.f;
@@ -307,19 +339,23 @@ SB_HD void project_bwd_one(const float* m, const float* s, float glob, const Cam
       v_vm[8 + j] += j02 * v_T0[j] + j12 * v_T1[j];
     }
   }
-  // Sigma = M M^T  ->  v_M = 2 G M
+}
+
+// Part B, per Gaussian: Sigma = M M^T with M = R(q / |q|) diag(glob * s)  ->  v_scale, v_quat from G = dL/dSigma.
+// Linear in G, so the fused multi-view backward sums G over the views first and runs this once.
+SB_HD void cov3d_chain_bwd(const float* s, float glob, const float* M, const float* R, const float* qn4,
+                           float qnorm, const float* G, float* v_scale, float* v_quat) {
   float vM[9];
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j)
       vM[3 * i + j] = 2.0f * (G[3 * i] * M[j] + G[3 * i + 1] * M[3 + j] + G[3 * i + 2] * M[6 + j]);
-  const float* R = f.R;
   const float sc[3] = {glob * s[0], glob * s[1], glob * s[2]};
   float vR[9];
   for (int j = 0; j < 3; ++j) {
     v_scale[j] = glob * (R[j] * vM[j] + R[3 + j] * vM[3 + j] + R[6 + j] * vM[6 + j]);
     for (int i = 0; i < 3; ++i) vR[3 * i + j] = vM[3 * i + j] * sc[j];
   }
-  const float qw = f.qn[0], qx = f.qn[1], qy = f.qn[2], qz = f.qn[3];
+  const float qw = qn4[0], qx = qn4[1], qy = qn4[2], qz = qn4[3];
   float vq[4];
   vq[0] = 2.0f * (-qz * vR[1] + qy * vR[2] + qz * vR[3] - qx * vR[5] - qy * vR[6] + qx * vR[7]);
   vq[1] = 2.0f * (qy * vR[1] + qz * vR[2] + qy * vR[3] - 2.0f * qx * vR[4] - qw * vR[5] + qz * vR[6]
@@ -330,46 +366,37 @@ SB_HD void project_bwd_one(const float* m, const float* s, float glob, const Cam
                   + qy * vR[5] + qx * vR[6] + qy * vR[7]);
   // through q / |q|
   const float dotp = qw * vq[0] + qx * vq[1] + qy * vq[2] + qz * vq[3];
-  const float inv_n = 1.0f / f.qnorm;
+  const float inv_n = 1.0f / qnorm;
   v_quat[0] = (vq[0] - qw * dotp) * inv_n;
   v_quat[1] = (vq[1] - qx * dotp) * inv_n;
   v_quat[2] = (vq[2] - qy * dotp) * inv_n;
   v_quat[3] = (vq[3] - qz * dotp) * inv_n;
 }
 
+SB_HD void project_bwd_one(const float* m, const float* s, float glob, const Cam& cam,
+                           const ProjFwd& f, float v_px, float v_py, float v_depth, float v_k0,
+                           float v_k1, float v_k2, float v_comp, const float* v_cov3d,
+                           float* v_mean, float* v_scale, float* v_quat, float* v_vm) {
+  float G[9];
+  project_bwd_view(m, f.cov3d, cam, f, v_px, v_py, v_depth, v_k0, v_k1, v_k2, v_comp, v_mean, G, v_vm);
+  if (v_cov3d) {
+    // direct cov3d gradient
+    G[0] += v_cov3d[0]; G[4] += v_cov3d[3]; G[8] += v_cov3d[5];
+    G[1] += 0.5f * v_cov3d[1]; G[3] += 0.5f * v_cov3d[1];
+    G[2] += 0.5f * v_cov3d[2]; G[6] += 0.5f * v_cov3d[2];
+    G[5] += 0.5f * v_cov3d[4]; G[7] += 0.5f * v_cov3d[4];
+  }
+  cov3d_chain_bwd(s, glob, f.M, f.R, f.qn, f.qnorm, G, v_scale, v_quat);
+}
+
 // cov3d-only forward/backward used when the near-plane test passed but the Gaussian is not
 // drawn (cov3d is still an API output with a gradient).
 SB_HD void cov3d_bwd_one(const float* s, float glob, const ProjFwd& f, const float* v_cov3d,
                          float* v_scale, float* v_quat) {
-  float G[9] = {v_cov3d[0], 0.5f * v_cov3d[1], 0.5f * v_cov3d[2],
-                0.5f * v_cov3d[1], v_cov3d[3], 0.5f * v_cov3d[4],
-                0.5f * v_cov3d[2], 0.5f * v_cov3d[4], v_cov3d[5]};
-  const float* M = f.M; const float* R = f.R;
-  float vM[9];
-  for (int i = 0; i < 3; ++i)
-    for (int j = 0; j < 3; ++j)
-      vM[3 * i + j] = 2.0f * (G[3 * i] * M[j] + G[3 * i + 1] * M[3 + j] + G[3 * i + 2] * M[6 + j]);
-  const float sc[3] = {glob * s[0], glob * s[1], glob * s[2]};
-  float vR[9];
-  for (int j = 0; j < 3; ++j) {
-    v_scale[j] = glob * (R[j] * vM[j] + R[3 + j] * vM[3 + j] + R[6 + j] * vM[6 + j]);
-    for (int i = 0; i < 3; ++i) vR[3 * i + j] = vM[3 * i + j] * sc[j];
-  }
-  const float qw = f.qn[0], qx = f.qn[1], qy = f.qn[2], qz = f.qn[3];
-  float vq[4];
-  vq[0] = 2.0f * (-qz * vR[1] + qy * vR[2] + qz * vR[3] - qx * vR[5] - qy * vR[6] + qx * vR[7]);
-  vq[1] = 2.0f * (qy * vR[1] + qz * vR[2] + qy * vR[3] - 2.0f * qx * vR[4] - qw * vR[5] + qz * vR[6]
-                  + qw * vR[7] - 2.0f * qx * vR[8]);
-  vq[2] = 2.0f * (-2.0f * qy * vR[0] + qx * vR[1] + qw * vR[2] + qx * vR[3] + qz * vR[5] - qw * vR[6]
-                  + qz * vR[7] - 2.0f * qy * vR[8]);
-  vq[3] = 2.0f * (-2.0f * qz * vR[0] - qw * vR[1] + qx * vR[2] + qw * vR[3] - 2.0f * qz * vR[4]
-                  + qy * vR[5] + qx * vR[6] + qy * vR[7]);
-  const float dotp = qw * vq[0] + qx * vq[1] + qy * vq[2] + qz * vq[3];
-  const float inv_n = 1.0f / f.qnorm;
-  v_quat[0] = (vq[0] - qw * dotp) * inv_n;
-  v_quat[1] = (vq[1] - qx * dotp) * inv_n;
-  v_quat[2] = (vq[2] - qy * dotp) * inv_n;
-  v_quat[3] = (vq[3] - qz * dotp) * inv_n;
+  const float G[9] = {v_cov3d[0], 0.5f * v_cov3d[1], 0.5f * v_cov3d[2],
+                      0.5f * v_cov3d[1], v_cov3d[3], 0.5f * v_cov3d[4],
+                      0.5f * v_cov3d[2], 0.5f * v_cov3d[4], v_cov3d[5]};
+  cov3d_chain_bwd(s, glob, f.M, f.R, f.qn, f.qnorm, G, v_scale, v_quat);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -149,3 +149,19 @@ def tile_lists_from_segments(gids_sorted, tile_bins, view, tiles_per_view):
     start_out = torch.cumsum(cnt, 0) - cnt
     pos = torch.arange(total) - start_out[tile_of] + bins[tile_of, 0]
     return gids_sorted.cpu()[pos], cnt
+
+
+def oracle_f64_grads(gs, cams, gt, views, masks=None, extra=None):
+    """Gradients of sum_v mean(|rgb_v - gt_v| * mask_v) (+ extra(rgb_v, v)) w.r.t. the raw parameters from the
+    FLOAT64 oracle -- the reference for every gradient tolerance (north_star: 1e-3 relative)."""
+    raw = {k: v.double().requires_grad_() for k, v in gs.items()}
+    kw = {k: cams[k] for k in ("cx", "cy", "fx", "fy", "width", "height", "background_color")}
+    loss = 0.0
+    for i, v in enumerate(views):
+        rgb, _ = R.render_view(raw, cams["camera_to_worlds"][v].double(), **kw)
+        m = 1.0 if masks is None else masks[i][..., None].double()
+        loss = loss + ((rgb - gt[v].double()).abs() * m).mean()
+        if extra is not None:
+            loss = loss + extra(rgb, v)
+    loss.backward()
+    return {k: p.grad for k, p in raw.items()}, float(loss.detach())

@@ -407,7 +407,7 @@ def test_stress_shaped_small_case_against_oracle(cuda, sb_lib):
     raw_ref = {k: v.clone().requires_grad_() for k, v in gs.items()}
     rgbs, alphas = gs_utils.rasterize_gaussians_to_multiimgs(raw, _dev(cams, cuda))
     assert render.last_num_intersects() > 10 * n
-    loss = loss_ref = 0.0
+    loss, masks = 0.0, []
     for v in range(2):
         rgb_ref, a_ref, aux = R.render_view(raw_ref, cams["camera_to_worlds"][v], cams["cx"], cams["cy"], cams["fx"],
                                             cams["fy"], cams["width"], cams["height"], cams["background_color"],
@@ -416,8 +416,9 @@ def test_stress_shaped_small_case_against_oracle(cuda, sb_lib):
         assert float((rgbs[v].detach().cpu() - rgb_ref.detach()).abs().amax(-1)[solid].max()) <= H.IMG_ATOL
         assert float((alphas[v].detach().cpu() - a_ref.detach()).abs()[solid].max()) <= H.IMG_ATOL
         m = solid[..., None].float()
-        loss_ref = loss_ref + ((rgb_ref - gt[v]).abs() * m).mean()
+        masks.append(solid)
         loss = loss + ((rgbs[v] - gt[v].to(cuda)).abs() * m.to(cuda)).mean()
-    loss.backward(); loss_ref.backward()
+    loss.backward()
+    ref, _ = H.oracle_f64_grads(gs, cams, gt, (0, 1), masks)
     for name in gs:
-        H.assert_grad_close(raw[name].grad, raw_ref[name].grad, name, rtol=5e-3)
+        H.assert_grad_close(raw[name].grad, ref[name], name, rtol=H.GRAD_RTOL)

@@ -193,7 +193,7 @@ def test_full_view_pipeline_matches_oracle(cuda, sb_lib):
     gt = synth.target_images(2, k["H"], k["W"], seed=9)
     raw_ref = {n_: v.clone().requires_grad_() for n_, v in gs.items()}
     raw = {n_: v.to(cuda).requires_grad_() for n_, v in gs.items()}
-    loss_ref, loss = 0.0, 0.0
+    loss_ref, loss, masks = 0.0, 0.0, []
     for view in range(2):
         rgb_ref, a_ref, aux = R.render_view(raw_ref, cams["camera_to_worlds"][view], cams["cx"], cams["cy"],
                                             cams["fx"], cams["fy"], cams["width"], cams["height"],
@@ -215,12 +215,14 @@ def test_full_view_pipeline_matches_oracle(cuda, sb_lib):
         err = (rgb.detach().cpu() - rgb_ref.detach()).abs().amax(-1)
         assert float(err[solid].max()) <= H.IMG_ATOL
         mask = solid[..., None].float()
+        masks.append(solid)
         loss_ref = loss_ref + ((rgb_ref - gt[view]).abs() * mask).mean()
         loss = loss + ((rgb - gt[view].to(cuda)).abs() * mask.to(cuda)).mean()
-    loss_ref.backward(); loss.backward()
+    loss.backward()
     assert abs(float(loss) - float(loss_ref)) < 1e-5
+    ref, _ = H.oracle_f64_grads(gs, cams, gt, (0, 1), masks)            # float64 oracle, same masked loss
     for name in gs:
-        H.assert_grad_close(raw[name].grad, raw_ref[name].grad, name, rtol=5e-3)
+        H.assert_grad_close(raw[name].grad, ref[name], name, rtol=H.GRAD_RTOL)
 
 
 @pytest.mark.parametrize("channels", [1, 2, 4, 7])

@@ -216,22 +216,26 @@ SB_API int sb_cov2d_bounds(int count, const float* cov2d, float* conics, int* ra
  * tile's segment [tile*capacity, (tile+1)*capacity).  sb_sort_tiles then sorts every segment and
  * writes gaussian_ids_sorted (same V*T*capacity indexing), tile_bins (V*T,2) = segment ranges
  * ((0,0) for empty tiles), view_has_isects (V, zero-filled by the caller) and totals (2 ints,
- * zero-filled): [0] = number of intersections, [1] = 1 if a tile held more than tile_capacity
- * Gaussians (its list is then truncated: the caller must redo the binning with the chain above).
+ * zero-filled): [0] = number of intersections, [1] = flags: bit 0 if a tile held more than tile_capacity
+ * Gaussians (its list is then truncated: the caller must redo the binning with the chain above), bit 1 if
+ * the rect-list pool ran out (see below).
  * tile_capacity: power of two in [64, sb_tile_sort_capacity()], V*T*capacity < 2^31. */
 SB_API int sb_tile_sort_capacity(void);
 SB_API int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, const int* tile_counts,
                   const uint64_t* tile_keys, int* gaussian_ids_sorted, int* tile_bins,
                   int* view_has_isects, int* totals, int n, int tiles_x, const float* packed,
-                  int* rect_ids, int* rect_counts, sb_stream_t stream);
+                  int* rect_ids, int* rect_meta, int* pool_head, int pool_capacity, sb_stream_t stream);
 
 /* ---- a10 / a11 for the fused path: rect-list rasteriser (block width 16 only) -------------
  * A 16x16 tile is eight 8x4-pixel rectangles (rect r: columns 8*(r&1).., rows 4*(r>>1)..).  Given
- * rect_ids (V*T*8*capacity) and rect_counts (V*T*8), sb_sort_tiles additionally writes, for every
- * rectangle, the depth-ordered ids of the Gaussians whose {alpha >= 1/255} region reaches it (exact
- * ellipse / rectangle test on the packed records, conservatively inflated) into
- * rect_ids[(tile*8 + r)*capacity + ...]
- * (gaussian_ids_sorted may then be NULL).  The two kernels below give each rectangle to one warp,
+ * rect_ids (a pool of pool_capacity ints, plus 32 ints of slack), rect_meta (V*T*8, 2) and pool_head (one
+ * int, zero-filled), sb_sort_tiles additionally writes, for every rectangle, the depth-ordered ids of the
+ * Gaussians whose {alpha >= 1/255} region reaches it (exact ellipse / rectangle test on the packed records,
+ * conservatively inflated) into the pool: rect_meta[rect] = (start, count), the list is
+ * rect_ids[start .. start + count).  A tile claims room for its eight lists with one atomic on *pool_head;
+ * if the pool runs out, bit 1 (value 2) of totals[1] is set, the tile's lists are left empty and *pool_head
+ * keeps counting, so that it reports the capacity the scene needs (gaussian_ids_sorted may be NULL when only
+ * the rect lists are wanted).  The two kernels below give each rectangle to one warp,
  * which walks its own list with no block-level synchronisation: same compositing order, same images
  * and gradients as sb_rasterize_fwd / _bwd (the dropped pairs are ones those kernels skip).
  * final_idx here is the position in the rectangle's list of the last composited Gaussian (-1: none);
@@ -240,13 +244,13 @@ SB_API int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, c
  * left at an unspecified value.  loss_partial here is (V, T, 8, 2): one (sum |rgb - gt|, sum (rgb - gt)^2)
  * pair per rectangle.  All other arguments as sb_rasterize_fwd / _bwd. */
 SB_API int sb_rasterize_rect_fwd(int num_views, int n, const float* packed, const int* rect_ids,
-                          const int* rect_counts, int rect_capacity, const float* background,
+                          const int* rect_meta, const float* background,
                           int img_h, int img_w, const int* view_has_isects, float* out_img,
                           float* final_ts, int* final_idx, float* out_alpha, int clamp_rgb_max1,
                           const void* gt, int gt_is_u8, float* loss_partial, int* work_counter,
                           sb_stream_t stream);
 SB_API int sb_rasterize_rect_bwd(int num_views, int n, const float* packed, const int* rect_ids,
-                          const int* rect_counts, int rect_capacity, const float* background,
+                          const int* rect_meta, const float* background,
                           int img_h, int img_w, const float* final_ts, const int* final_idx,
                           const float* v_out_img, const float* v_out_alpha, const float* out_img,
                           int clamped_rgb_max1, const void* gt, int gt_is_u8, const float* v_loss,

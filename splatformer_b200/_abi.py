@@ -56,9 +56,9 @@ SIGNATURES = {
     "sb_views_project_fwd": (I, [I, I, P, P, F, P, P, P, P, I, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P,
                                  P, P, I, P]),
     "sb_tile_sort_capacity": (I, []),
-    "sb_sort_tiles": (I, [I, I, I, P, P, P, P, P, P, I, I, P, P, P, P]),
-    "sb_rasterize_rect_fwd": (I, [I, I, P, P, P, I, P, I, I, P, P, P, P, P, I, P, I, P, P, P]),
-    "sb_rasterize_rect_bwd": (I, [I, I, P, P, P, I, P, I, I, P, P, P, P, P, I, P, I, P, P, P]),
+    "sb_sort_tiles": (I, [I, I, I, P, P, P, P, P, P, I, I, P, P, P, P, I, P]),
+    "sb_rasterize_rect_fwd": (I, [I, I, P, P, P, P, I, I, P, P, P, P, P, I, P, I, P, P, P]),
+    "sb_rasterize_rect_bwd": (I, [I, I, P, P, P, P, I, I, P, P, P, P, P, I, P, I, P, P, P]),
     "sb_views_project_bwd": (I, [I, I, P, P, F, P, I, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P, P, P, P,
                                  P, P, P]),
 }

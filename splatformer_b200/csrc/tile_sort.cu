@@ -58,11 +58,13 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
                                                                 int* __restrict__ gids_sorted, int2* __restrict__ bins,
                                                                 int* __restrict__ view_has, int* __restrict__ totals,
                                                                 int n, int tiles_x, const float4* __restrict__ packed,
-                                                                int* __restrict__ rect_ids, int* __restrict__ rect_counts) {
+                                                                int* __restrict__ rect_ids, int2* __restrict__ rect_meta,
+                                                                int* __restrict__ pool_head, int pool_cap) {
   extern __shared__ unsigned long long s_keys[];
   int* s_end = reinterpret_cast<int*>(s_keys + cap);
   __shared__ unsigned s_min, s_max;
   __shared__ int s_warp[kSortBlock / 32], s_overflow;
+  __shared__ int s_rcnt[8], s_roff[8], s_base;
   const int count = __ldg(counts + blockIdx.x);
   const int len = min(count, cap);
   const int2 range = make_int2(blockIdx.x * cap, blockIdx.x * cap + len);       // V*T*cap < 2^31 (host checks)
@@ -70,10 +72,10 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
     // empty tiles keep (0, 0) like upstream's zero-initialised tile_bins
     bins[blockIdx.x] = len > 0 ? range : make_int2(0, 0);
     if (len > 0) { view_has[blockIdx.x / tiles_per_view] = 1; atomicAdd(totals, len); }
-    if (count > cap) totals[1] = 1;
+    if (count > cap) atomicOr(totals + 1, 1);
   }
   if (len <= 0) {
-    if (rect_counts && threadIdx.x < 8) rect_counts[(size_t)blockIdx.x * 8 + threadIdx.x] = 0;
+    if (rect_meta && threadIdx.x < 8) rect_meta[(size_t)blockIdx.x * 8 + threadIdx.x] = make_int2(0, 0);
     return;
   }
   const unsigned long long* src = keys + range.x;
@@ -180,24 +182,58 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
   // whose visible region reaches it (raster_common.cuh: rect_mask), compacted stably per rectangle into
   // rect_ids[(tile * 8 + r) * cap + ...]; the rect-list rasteriser gives every rectangle to one warp.
   // Phase A: every entry's 8-bit rectangle mask into shared memory (the bucket table s_end is free by now).
-  // Phase B: warp r owns rectangle r and walks the masks in list order, 32 entries per step: one ballot on
-  // bit r, the set lanes store their ids behind the warp's running offset -- stable, no counts to scan.
+  // Phase B: stable compaction of the ids into the eight lists.
   unsigned char* s_mask = reinterpret_cast<unsigned char*>(s_end);
   const int v = blockIdx.x / tiles_per_view, tile = blockIdx.x - v * tiles_per_view;
   const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
   const float4* vp = packed + (size_t)v * n * 3;
+  if (threadIdx.x < 8) s_rcnt[threadIdx.x] = 0;
   __syncthreads();                                 // everyone is done with s_end as the bucket table
-  for (int i = threadIdx.x; i < len; i += kSortBlock) {
-    const float4* rec = vp + (size_t)(unsigned)(s_keys[i] & 0xffffffffull) * 3;
-    s_mask[i] = (unsigned char)rect_mask(__ldg(rec), __ldg(rec + 1), tile_x, tile_y);
+  {
+    // the rectangles' list lengths are counted on the way: one vote per rectangle and 32 entries, lane r keeps
+    // rectangle r's running count (the lists go into a POOL shared by all tiles -- no per-rectangle capacity, a
+    // list takes exactly its length -- so the lengths must be known before anything is stored)
+    int my_cnt = 0;
+    for (int i0 = 0; i0 < len; i0 += kSortBlock) {
+      const int i = i0 + threadIdx.x;
+      unsigned m = 0u;
+      if (i < len) {
+        const float4* rec = vp + (size_t)(unsigned)(s_keys[i] & 0xffffffffull) * 3;
+        m = rect_mask(__ldg(rec), __ldg(rec + 1), tile_x, tile_y);
+        s_mask[i] = (unsigned char)m;
+      }
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const int c = __popc(__ballot_sync(0xffffffffu, (m >> r) & 1u));
+        if (lane == r) my_cnt += c;
+      }
+    }
+    if (lane < 8 && my_cnt) atomicAdd(&s_rcnt[lane], my_cnt);
   }
   __syncthreads();
   {
+    // the tile claims room for its eight lists with one atomic on the pool head; then warp r owns rectangle r and
+    // walks the masks in list order, 32 entries per step: one ballot on bit r, the set lanes store their ids
+    // behind the warp's running offset -- stable
     const int r = warp;                            // kSortBlock / 32 == 8 rectangles
-    int* out = rect_ids + ((size_t)blockIdx.x * 8 + r) * cap;
+    static_assert(kSortBlock == 8 * 32, "one warp per rectangle");
+    if (threadIdx.x == 0) {
+      int tot = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { s_roff[k] = tot; tot += s_rcnt[k]; }
+      int base = tot > 0 ? atomicAdd(pool_head, tot) : 0;        // (keeps counting past the end: the host learns the need)
+      if (base + tot > pool_cap) { base = -1; atomicOr(totals + 1, 2); }
+      s_base = base;
+    }
+    __syncthreads();
+    const int cnt = s_rcnt[r];
+    const int base = s_base;
+    const int start = base < 0 ? 0 : base + s_roff[r];
+    if (lane == 0) rect_meta[(size_t)blockIdx.x * 8 + r] = make_int2(start, base < 0 ? 0 : cnt);
+    if (base < 0) return;
+    int* out = rect_ids + start;
     const unsigned lt = (1u << lane) - 1u;
     int off = 0;
-    static_assert(kSortBlock == 8 * 32, "one warp per rectangle");
 #pragma unroll 4
     for (int i0 = 0; i0 < len; i0 += 32) {
       const int i = i0 + lane;
@@ -206,7 +242,6 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
       if (hit) out[off + __popc(bal & lt)] = (int)(unsigned)(s_keys[i] & 0xffffffffull);
       off += __popc(bal);
     }
-    if (lane == 0) rect_counts[(size_t)blockIdx.x * 8 + r] = off;
   }
 }
 
@@ -217,11 +252,13 @@ extern "C" int sb_tile_sort_capacity(void) { return sb::kMaxSegment; }
 extern "C" int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, const int* tile_counts,
                              const uint64_t* tile_keys, int* gaussian_ids_sorted, int* tile_bins,
                              int* view_has_isects, int* totals, int n, int tiles_x, const float* packed,
-                             int* rect_ids, int* rect_counts, sb_stream_t stream) {
+                             int* rect_ids, int* rect_meta, int* pool_head, int pool_capacity,
+                             sb_stream_t stream) {
   if (num_views < 1 || tiles_per_view < 1 || tile_capacity < 64 || tile_capacity > sb::kMaxSegment ||
       (tile_capacity & (tile_capacity - 1)) ||
       (long long)num_views * tiles_per_view * tile_capacity > 2147483647LL ||
-      (rect_ids && ((!packed && n > 0) || !rect_counts || tiles_x < 1 || tiles_per_view % tiles_x)))
+      (rect_ids && ((!packed && n > 0) || !rect_meta || !pool_head || pool_capacity < 1 || tiles_x < 1 ||
+                    tiles_per_view % tiles_x)))
     return SB_ERR_BAD_ARG;
   const size_t smem = (size_t)tile_capacity * 12;
   if (smem > 40 * 1024)      // the kernel also has a little static shared memory
@@ -229,6 +266,6 @@ extern "C" int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacit
   sb::sort_tiles_kernel<<<num_views * tiles_per_view, sb::kSortBlock, smem, (cudaStream_t)stream>>>(
       tile_capacity, tiles_per_view, tile_counts, reinterpret_cast<const unsigned long long*>(tile_keys),
       gaussian_ids_sorted, reinterpret_cast<int2*>(tile_bins), view_has_isects, totals, n, tiles_x,
-      reinterpret_cast<const float4*>(packed), rect_ids, rect_counts);
+      reinterpret_cast<const float4*>(packed), rect_ids, reinterpret_cast<int2*>(rect_meta), pool_head, pool_capacity);
   SB_RETURN_LAST();
 }

@@ -104,8 +104,9 @@ GLOBAL_SORT_TILES_PER_GAUSSIAN = 16.0
 
 
 class _Totals:
-    """The two ints the tile sort reports -- [0] intersections, [1] overflow flag -- on their way to the
-    host: a pinned buffer, the event after which it is valid, and the plan entry they belong to."""
+    """The three ints the tile sort reports -- intersections, overflow flags (bit 0: a tile segment, bit 1: the
+    rect-list pool), rect-list entries -- on their way to the host: a pinned buffer, the event after which it is
+    valid, and the plan entry they belong to."""
 
     __slots__ = ("host", "event", "key", "plan", "value", "folded")
 
@@ -115,11 +116,11 @@ class _Totals:
     def ready(self) -> bool:
         return self.value is not None or self.event.query()
 
-    def read(self) -> Tuple[int, int]:
-        """(intersections, overflow); waits for the device to have produced them."""
+    def read(self) -> Tuple[int, int, int]:
+        """(intersections, overflow flags, rect-list entries); waits for the device to have produced them."""
         if self.value is None:
             self.event.synchronize()
-            self.value = (int(self.host[0]), int(self.host[1]))
+            self.value = (int(self.host[0]), int(self.host[1]), int(self.host[2]))
         if not self.folded:
             self.folded = True
             self.plan._fold(self.key, *self.value)
@@ -140,6 +141,7 @@ class RenderPlan:
         self.last: Optional[_Totals] = None
         self.replays = 0
         self.seen: set = set()               # shapes whose first call (read synchronously) is behind us
+        self.pool_used: Dict[Tuple[int, int, int], int] = {}     # rect-list entries the shape's scenes needed so far
         self._slots: List[Tensor] = []       # pinned (2,) int32 landing buffers of the totals, recycled
         self._slot_users: List[Optional[_Totals]] = []
 
@@ -154,7 +156,7 @@ class RenderPlan:
                 idx = i
                 break
         if idx is None and len(self._slots) < 16:
-            self._slots.append(torch.zeros(2, dtype=I32).pin_memory())
+            self._slots.append(torch.zeros(3, dtype=I32).pin_memory())
             self._slot_users.append(None)
             idx = len(self._slots) - 1
         if idx is None:
@@ -178,6 +180,15 @@ class RenderPlan:
             return 0
         return cap
 
+    def pool_capacity(self, key, cap: int) -> int:
+        """Ints to reserve for the rect lists of a pass: 1.3 x what the shape's scenes needed so far, or, before
+        anything is known, 12 per (view, Gaussian) -- never more than the fixed-capacity layout would take."""
+        v, num_tiles, n = key
+        ceiling = v * num_tiles * 8 * cap
+        used = self.pool_used.get(key)
+        want = int(used * 1.3) + (1 << 20) if used else max(12 * v * n, 1 << 20)
+        return max(1024, min(ceiling, (want + (1 << 20) - 1) >> 20 << 20))
+
     def poll(self) -> None:
         """Fold in the totals of earlier calls that have reached the host by now (never blocks)."""
         keep = []
@@ -188,9 +199,11 @@ class RenderPlan:
                 keep.append(t)
         self.pending = keep
 
-    def _fold(self, key, num_intersects: int, overflow: int) -> None:
-        if overflow:
+    def _fold(self, key, num_intersects: int, overflow: int, pool_used: int = 0) -> None:
+        if overflow & 1:
             self.overflowed[key] = self.overflowed.get(key, 0) + 1
+        if pool_used > 0:
+            self.pool_used[key] = max(self.pool_used.get(key, 0), pool_used)
         v, _, n = key
         if num_intersects > GLOBAL_SORT_TILES_PER_GAUSSIAN * v * n:
             self.prefer_global[key] = True
@@ -246,7 +259,7 @@ class _Pass:
         self.tiles_hit = torch.empty(v, n, dtype=I32, device=dev)
         self.out_img = self.final_ts = self.final_idx = self.out_alpha = None
         self.loss_sums = None           # (V, 2) per-view sums of |rgb - gt| and (rgb - gt)^2, updated in place on a replay
-        self.gids_sorted = self.tile_bins = self.rect_ids = self.rect_counts = None
+        self.gids_sorted = self.tile_bins = self.rect_ids = self.rect_meta = None
         self.cap = 0
 
     # ---- buffers -------------------------------------------------------------------------------
@@ -300,7 +313,7 @@ class _Pass:
         with _stage("raster_fwd"):
             _abi.check(lib.sb_rasterize_rect_fwd(
                 self.v, self.n, p(self.packed, F32, "packed"), p(self.rect_ids, I32, "rect_ids"),
-                p(self.rect_counts, I32, "rect_counts"), self.cap, p(self.background, F32, "background"),
+                p(self.rect_meta, I32, "rect_meta"), p(self.background, F32, "background"),
                 self.h, self.w, p(view_has, I32, "view_has_isects"),
                 p(self.out_img, F32, "out_img"), p(self.final_ts, F32, "final_Ts"),
                 p(self.final_idx, I32, "final_idx"), p(self.out_alpha, F32, "out_alpha"),
@@ -333,26 +346,30 @@ class _Pass:
         self.cap = cap
         with _stage("zero_counts"):
             state = torch.zeros(v * num_tiles + v + 4, dtype=I32, device=dev)
-        tile_counts, view_has, totals = state[:v * num_tiles], state[v * num_tiles:-4], state[-4:-2]
-        work = state[-2:]               # rectangle queue heads of the persistent raster kernels
+        tile_counts, view_has = state[:v * num_tiles], state[v * num_tiles:-4]
+        totals = state[-4:-1]           # intersections, overflow flags, rect-list pool head (= entries needed)
+        work = state[-1:]               # rectangle queue head of the persistent raster kernel
         tile_keys = torch.empty(v * num_tiles * cap, dtype=torch.int64, device=dev)
         self.project(tile_counts, tile_keys, cap)
         self.alloc_images()
         self.gids_sorted = torch.empty(v * num_tiles * cap, dtype=I32, device=dev)
         self.tile_bins = torch.empty(v * num_tiles, 2, dtype=I32, device=dev)
         use_rect = self.bw == 16 and USE_RECT_LISTS
+        pool_cap = 0
         if use_rect:
-            # per-rectangle lists for the rect-list rasteriser (one warp per 8x4 rectangle)
-            self.rect_ids = torch.empty(v * num_tiles * 8 * cap, dtype=I32, device=dev)
-            self.rect_counts = torch.empty(v * num_tiles * 8, dtype=I32, device=dev)
+            # per-rectangle lists for the rect-list rasteriser (one warp per 8x4 rectangle), packed into one pool
+            pool_cap = plan.pool_capacity((v, num_tiles, self.n), cap)
+            self.rect_ids = torch.empty(pool_cap + 32, dtype=I32, device=dev)
+            self.rect_meta = torch.empty(v * num_tiles * 8, 2, dtype=I32, device=dev)
         with _stage("sort_tiles"):
             _abi.check(lib.sb_sort_tiles(
                 v, num_tiles, cap, p(tile_counts, I32, "tile_counts"),
                 p(tile_keys, torch.int64, "tile_keys"), p(self.gids_sorted, I32, "gaussian_ids_sorted"),
                 p(self.tile_bins, I32, "tile_bins"), p(view_has, I32, "view_has_isects"),
                 p(totals, I32, "totals"), self.n, self.tiles_x, p(self.packed, F32, "packed"),
-                p(self.rect_ids, I32, "rect_ids"), p(self.rect_counts, I32, "rect_counts"),
-                self.st), "sb_sort_tiles")
+                p(self.rect_ids, I32, "rect_ids"), p(self.rect_meta, I32, "rect_meta"),
+                p(totals[2:] if use_rect else None, I32, "pool_head"), pool_cap, self.st), "sb_sort_tiles")
+
         def landed(host_totals):
             host_totals.copy_(totals, non_blocking=True)
             ready = torch.cuda.Event()
@@ -361,7 +378,7 @@ class _Pass:
         result = plan.host_slot(landed)
         # the raster kernel is enqueued optimistically: the device produced the flag BEFORE it starts
         if use_rect:
-            self.raster_rect(view_has, work[:1])
+            self.raster_rect(view_has, work)
         else:
             self.raster_tiles(view_has)
         return result
@@ -373,14 +390,14 @@ class _Pass:
             self.project(None, None, 0)
         self.alloc_images()
         self.cap = 0
-        self.rect_ids = self.rect_counts = None
+        self.rect_ids = self.rect_meta = None
         with _stage("global_sort"):
             num_intersects, _, self.gids_sorted, self.tile_bins, view_ends = utils.bin_depth_ordered(
                 self.v, self.n, self.packed, 12, self.depths.view(-1), self.radii.view(-1), self.tiles_hit,
                 (self.tiles_x, self.tiles_y, 1), self.bw, compact=True)
         view_has = (torch.diff(view_ends, prepend=view_ends.new_zeros(1)) > 0).to(I32)
         self.raster_tiles(view_has)
-        return _Totals(None, None, (self.v, self.num_tiles, self.n), plan, value=(num_intersects, 0))
+        return _Totals(None, None, (self.v, self.num_tiles, self.n), plan, value=(num_intersects, 0, 0))
 
 
 def grad_layout(n: int, color_shape, rest_shape) -> Tuple[List[Tuple[str, int, Tuple[int, ...]]], int]:
@@ -514,7 +531,7 @@ class _RenderViews(Function):
             st = _abi.stream()
             ps.st = st
             # the binning flag of the forward: the device wrote it before the forward rasteriser started
-            num_intersects, overflow = ctx.totals.read()
+            num_intersects, overflow, _ = ctx.totals.read()
             if overflow:
                 # a tile ran over its segment: the lists the forward walked were truncated.  Redo the pass with
                 # the global sort over the same buffers (images and loss sums are corrected in place), then
@@ -538,7 +555,7 @@ class _RenderViews(Function):
                 with _stage("raster_bwd"):
                     _abi.check(lib.sb_rasterize_rect_bwd(
                         v, n, p(ps.packed, F32, "packed"), p(ps.rect_ids, I32, "rect_ids"),
-                        p(ps.rect_counts, I32, "rect_counts"), ps.cap, p(ps.background, F32, "background"),
+                        p(ps.rect_meta, I32, "rect_meta"), p(ps.background, F32, "background"),
                         ps.h, ps.w, p(ps.final_ts, F32, "final_Ts"),
                         p(ps.final_idx, I32, "final_idx"), p(v_out_img, F32, "v_out_img"),
                         p(v_out_alpha, F32, "v_out_alpha"), p(out_img, F32, "out_img"),

@@ -54,7 +54,7 @@ def test_no_torch_types_or_cpu_fallback_in_the_boundary():
     assert lib.sb_sort_pairs(-1, 40, None, None, None, None, None, 0, None) == -1
     assert lib.sb_rasterize_fwd(1, 0, None, None, None, None, 16, 16, 17, None, None, None, None, None, 0, None, 0,
                                 None, None) == -1           # block_width 17
-    assert lib.sb_sort_tiles(1, 64, 100, None, None, None, None, None, None, 0, 0, None, None, None, None) == -1    # capacity not a power of two
+    assert lib.sb_sort_tiles(1, 64, 100, None, None, None, None, None, None, 0, 0, None, None, None, None, 0, None) == -1    # capacity not a power of two
     assert lib.sb_sh_fwd(1, 4, 2, 3, None, None, None, None) == -1      # degrees_to_use > degree
 
 

@@ -335,7 +335,7 @@ def test_fused_l1_plus_image_space_loss(cuda, sb_lib):
     rgb3, _ = gs_utils.render_scene(raw3, **{k_: v.to(cuda) for k_, v in cams.items()})
     (0.5 * ((rgb3 - gt.to(cuda)) ** 2 * wgt.to(cuda)).mean(dim=(1, 2, 3)).sum()).backward()
     for name in gs:
-        assert H.rel_l2(raw2[name].grad, raw3[name].grad) <= 1e-5, name
+        assert H.rel_l2(raw2[name].grad, raw3[name].grad) <= 5e-5, name      # (summation order of the atomics)
 
 
 def test_render_views_argument_conventions(cuda, sb_lib):

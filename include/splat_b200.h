@@ -123,11 +123,8 @@ SB_API int sb_map_gaussian_to_tiles_ordered(int num_views, int n, const float* x
                                      const float* depths, const int* radii, const int* order,
                                      const int* cum_tiles_hit_ordered, int tiles_x, int tiles_y,
                                      int block_width, uint32_t* tile_ids, int* gaussian_ids,
-                                     uint32_t* digit_hist, int hist_passes, sb_stream_t stream);
-/* digit_hist (may be NULL): [hist_passes][256] uint32, zero-filled by the caller; the emission adds, for each
- * of the hist_passes (1..4) low bytes of the tile index, the number of emitted pairs per byte value -- the
- * histograms sb_sort_tiles_global would otherwise take with a read of its own.
- * sb_sort_tiles_global: stable sort of the (tile index, Gaussian id) pairs on the tile index
+                                     sb_stream_t stream);
+/* sb_sort_tiles_global: stable sort of the (tile index, Gaussian id) pairs on the tile index
  * (num_tiles_total = V*T distinct values), keeping ONLY the sorted ids (the key is implied by the bin); the
  * last sweep counts the pairs per tile, and a single-pass scan + one elementwise kernel inside the same call
  * turn the counts into tile_bins (num_tiles_total, 2), (0,0) for empty tiles.

@@ -39,7 +39,7 @@ SIGNATURES = {
     "sb_gather_i32": (I, [I, P, P, P, P]),
     "sb_map_gaussian_to_intersects_ordered": (I, [I, I, P, I, P, P, P, P, I, I, I, P, P, P]),
     "sb_sort_pairs_range": (I, [I, I, I, P, P, P, P, P, S, P]),
-    "sb_map_gaussian_to_tiles_ordered": (I, [I, I, P, I, P, P, P, P, I, I, I, P, P, P, I, P]),
+    "sb_map_gaussian_to_tiles_ordered": (I, [I, I, P, I, P, P, P, P, I, I, I, P, P, P]),
     "sb_sort_tiles_global_temp_bytes": (S, [I, I]),
     "sb_sort_tiles_global": (I, [I, I, P, P, P, P, P, P, S, P]),
     "sb_sort32_temp_bytes": (S, [I]),

@@ -15,22 +15,12 @@ constexpr int kCoopTiles = 8;
 
 // COMPACT: the key is the 32-bit tile index alone (depth-ordered emission: the depth is already encoded in
 // the position), stored through the same pointer reinterpreted as uint32.
-// COMPACT with digit_hist: the kernel also counts, for each of the `hist_passes` low bytes of the tile index,
-// how many emitted pairs carry each byte value ([hist_passes][256], zero on entry) -- the digit histograms the
-// one-sweep radix sort needs, taken here while the keys are in registers instead of by another read.
 template <bool COMPACT>
 __global__ void __launch_bounds__(256) map_isect_kernel(
     int num_views, int n, const float* __restrict__ xys, int xy_stride, const float* __restrict__ depths,
     const int* __restrict__ radii, const int* __restrict__ cum, int tiles_x, int tiles_y, int bw,
-    int64_t* __restrict__ keys, int* __restrict__ gids, const int* __restrict__ order,
-    unsigned* __restrict__ digit_hist, int hist_passes) {
+    int64_t* __restrict__ keys, int* __restrict__ gids, const int* __restrict__ order) {
   uint32_t* keys32 = reinterpret_cast<uint32_t*>(keys);
-  __shared__ unsigned s_hist[4][256];
-  const bool do_hist = COMPACT && digit_hist != nullptr;
-  if (do_hist) {
-    for (int i = threadIdx.x; i < hist_passes * 256; i += 256) (&s_hist[0][0])[i] = 0u;
-    __syncthreads();
-  }
   // slot j of the emission order handles (view, Gaussian) index i = order[j] (identity without `order`);
   // cum is the prefix sum of the tile counts in emission order
   const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;
@@ -61,10 +51,6 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
       const int64_t t = tile0 + (int64_t)(min_y + ky) * tiles_x + (min_x + kx);
       if (COMPACT) keys32[k + e] = (uint32_t)t; else keys[k + e] = (t << 32) | depth_bits;
       gids[k + e] = g;
-      if (do_hist) {
-        // (lanes walk different Gaussians here: their tiles are unrelated, plain shared atomics)
-        for (int p = 0; p < hist_passes; ++p) atomicAdd(&s_hist[p][((uint32_t)t >> (8 * p)) & 255u], 1u);
-      }
     }
   }
   unsigned big = __ballot_sync(0xffffffffu, total > kCoopTiles);
@@ -86,27 +72,6 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
         if (COMPACT) keys32[s_k + e] = (uint32_t)t; else keys[s_k + e] = (t << 32) | s_depth;
         gids[s_k + e] = s_g;
       }
-      if (do_hist) {
-        // consecutive lanes = consecutive tiles of a row: the high bytes usually coincide across the warp -- one
-        // vote finds that out and lane 0 adds the whole group; otherwise plain shared atomics (no MATCH.ANY,
-        // see radix_sort.cu)
-        for (int p = 0; p < hist_passes; ++p) {
-          const unsigned d = ((uint32_t)t >> (8 * p)) & 255u;
-          const unsigned d0 = __shfl_sync(0xffffffffu, d, 0);
-          if (__all_sync(0xffffffffu, on && d == d0)) {
-            if (lane == 0) atomicAdd(&s_hist[p][d], 32u);
-          } else if (on) {
-            atomicAdd(&s_hist[p][d], 1u);
-          }
-        }
-      }
-    }
-  }
-  if (do_hist) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < hist_passes * 256; i += 256) {
-      const unsigned c = (&s_hist[0][0])[i];
-      if (c) atomicAdd(digit_hist + i, c);
     }
   }
 }
@@ -170,7 +135,7 @@ extern "C" int sb_map_gaussian_to_intersects(int num_views, int n, const float* 
   if (total == 0) return 0;
   sb::map_isect_kernel<false><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit, tiles_x, tiles_y, block_width, isect_ids,
-      gaussian_ids, nullptr, nullptr, 0);
+      gaussian_ids, nullptr);
   SB_RETURN_LAST();
 }
 
@@ -185,7 +150,7 @@ extern "C" int sb_map_gaussian_to_intersects_ordered(int num_views, int n, const
   if (total == 0) return 0;
   sb::map_isect_kernel<false><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit_ordered, tiles_x, tiles_y, block_width, isect_ids,
-      gaussian_ids, order, nullptr, 0);
+      gaussian_ids, order);
   SB_RETURN_LAST();
 }
 
@@ -193,15 +158,14 @@ extern "C" int sb_map_gaussian_to_tiles_ordered(int num_views, int n, const floa
                                                 const float* depths, const int* radii, const int* order,
                                                 const int* cum_tiles_hit_ordered, int tiles_x, int tiles_y,
                                                 int block_width, uint32_t* tile_ids, int* gaussian_ids,
-                                                uint32_t* digit_hist, int hist_passes, sb_stream_t stream) {
-  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || xys_stride < 2 || (xys_stride & 1) || !order ||
-      (digit_hist && (hist_passes < 1 || hist_passes > 4)))
+                                                sb_stream_t stream) {
+  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || xys_stride < 2 || (xys_stride & 1) || !order)
     return SB_ERR_BAD_ARG;
   const size_t total = (size_t)num_views * n;
   if (total == 0) return 0;
   sb::map_isect_kernel<true><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit_ordered, tiles_x, tiles_y, block_width,
-      reinterpret_cast<int64_t*>(tile_ids), gaussian_ids, order, digit_hist, hist_passes);
+      reinterpret_cast<int64_t*>(tile_ids), gaussian_ids, order);
   SB_RETURN_LAST();
 }
 

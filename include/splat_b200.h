@@ -218,6 +218,12 @@ SB_API int sb_cov2d_bounds(int count, const float* cov2d, float* conics, int* ra
  * the rect-list pool ran out (see below).
  * tile_capacity: power of two in [64, sb_tile_sort_capacity()], V*T*capacity < 2^31. */
 SB_API int sb_tile_sort_capacity(void);
+/* The same binning for Gaussians that were projected by an earlier sb_project_fwd call (what
+ * gsplat.rasterize_gaussians receives, gs_utils.py:96-109): xys / depths / radii (V,N,..) -> slot claims in
+ * tile_counts (V*T, zero-filled) and keys in tile_keys (V*T*tile_capacity), then sb_sort_tiles as above. */
+SB_API int sb_bin_to_tile_segments(int num_views, int n, const float* xys, int xys_stride, const float* depths,
+                            const int* radii, int tiles_x, int tiles_y, int block_width, int* tile_counts,
+                            uint64_t* tile_keys, int tile_capacity, sb_stream_t stream);
 SB_API int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, const int* tile_counts,
                   const uint64_t* tile_keys, int* gaussian_ids_sorted, int* tile_bins,
                   int* view_has_isects, int* totals, int n, int tiles_x, const float* packed,

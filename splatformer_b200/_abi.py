@@ -56,6 +56,7 @@ SIGNATURES = {
     "sb_views_project_fwd": (I, [I, I, P, P, F, P, P, P, P, I, I, P, I, P, F, F, F, F, P, I, I, I, F, P, P, P, P,
                                  P, P, I, P]),
     "sb_tile_sort_capacity": (I, []),
+    "sb_bin_to_tile_segments": (I, [I, I, P, I, P, P, I, I, I, P, P, I, P]),
     "sb_sort_tiles": (I, [I, I, I, P, P, P, P, P, P, I, I, P, P, P, P, I, P]),
     "sb_rasterize_rect_fwd": (I, [I, I, P, P, P, P, I, I, P, P, P, P, P, I, P, I, P, P, P]),
     "sb_rasterize_rect_bwd": (I, [I, I, P, P, P, P, I, I, P, P, P, P, P, I, P, I, P, P, P]),

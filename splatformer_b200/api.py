@@ -157,6 +157,12 @@ def _pack(xys: Tensor, conics: Tensor, colors: Tensor, opacity: Tensor) -> Tenso
     return packed
 
 
+# Segment capacity / rect-list pool of the per-view rect path (block width 16).  A frame whose tiles are deeper,
+# or whose lists need more room, is detected through the totals the tile sort reports and takes the global path.
+RECT_TILE_CAPACITY = 2048
+USE_RECT_PATH = True
+
+
 class _RasterizeGaussians(Function):
     @staticmethod
     def forward(ctx, xys, depths, radii, conics, num_tiles_hit, colors, opacity, img_height,
@@ -167,8 +173,10 @@ class _RasterizeGaussians(Function):
         channels = colors.shape[-1]
         tiles_x = (img_width + block_width - 1) // block_width
         tiles_y = (img_height + block_width - 1) // block_width
-        num_intersects, cum_tiles_hit = utils.compute_cumulative_intersects(num_tiles_hit)
-        if num_intersects < 1:
+        groups = _channel_groups(channels)
+        p = _abi.ptr
+
+        def empty_frame():
             out_img = torch.ones(img_height, img_width, channels, dtype=F32, device=dev) * background
             final_ts = torch.zeros(img_height, img_width, dtype=F32, device=dev)
             ctx.empty = True
@@ -176,37 +184,83 @@ class _RasterizeGaussians(Function):
             ctx.set_materialize_grads(False)
             out_alpha = 1 - final_ts
             return (out_img, out_alpha) if return_alpha else out_img
-        xys, conics, colors = _f(xys), _f(conics), _f(colors)
-        opacity = _f(opacity).view(-1)
-        (_, _, _, gaussian_ids_sorted, tile_bins) = utils.bin_and_sort_gaussians(
-            n, num_intersects, xys, _f(depths), _f(radii), cum_tiles_hit, (tiles_x, tiles_y, 1),
-            block_width)
-        background = _f(background.to(F32))
+
+        xys_c, conics_c, colors_c = _f(xys), _f(conics), _f(colors)
+        opacity_c = _f(opacity).view(-1)
+        background_c = _f(background.to(F32))
+        rect_ids = rect_meta = gaussian_ids_sorted = tile_bins = None
+        packs = None
+        num_intersects = -1
+        num_tiles = tiles_x * tiles_y
+        cap = RECT_TILE_CAPACITY
+        if USE_RECT_PATH and block_width == 16 and n > 0 and num_tiles * cap < 2 ** 31:
+            # Per-tile segments + per-tile depth sort + rect lists (csrc/tile_sort.cu), as the fused path: no prefix
+            # sum, no emission, no 64-bit global sort, no bin-edge pass; the one host read (intersection count and
+            # overflow flags) takes the place of upstream's cum_tiles_hit[-1].item().
+            st = _abi.stream()
+            packs = [_pack(xys_c, conics_c, _group3(colors_c, lo, width), opacity_c) for lo, width in groups]
+            state = torch.zeros(num_tiles + 1 + 4, dtype=I32, device=dev)
+            tile_counts, view_has, totals, work = state[:num_tiles], state[num_tiles:-4], state[-4:-1], state[-1:]
+            tile_keys = torch.empty(num_tiles * cap, dtype=torch.int64, device=dev)
+            _abi.check(lib.sb_bin_to_tile_segments(
+                1, n, p(xys_c, F32, "xys"), 2, p(_f(depths), F32, "depths"), p(_f(radii), I32, "radii"), tiles_x,
+                tiles_y, block_width, p(tile_counts, I32, "tile_counts"), p(tile_keys, torch.int64, "tile_keys"), cap,
+                st), "sb_bin_to_tile_segments")
+            pool_cap = int(min(num_tiles * 8 * cap, max(12 * n, 1 << 18)))
+            rect_ids = torch.empty(pool_cap + 32, dtype=I32, device=dev)
+            rect_meta = torch.empty(num_tiles * 8, 2, dtype=I32, device=dev)
+            tile_bins = torch.empty(num_tiles, 2, dtype=I32, device=dev)
+            _abi.check(lib.sb_sort_tiles(
+                1, num_tiles, cap, p(tile_counts, I32, "tile_counts"), p(tile_keys, torch.int64, "tile_keys"), None,
+                p(tile_bins, I32, "tile_bins"), p(view_has, I32, "view_has_isects"), p(totals, I32, "totals"), n,
+                tiles_x, p(packs[0], F32, "packed"), p(rect_ids, I32, "rect_ids"), p(rect_meta, I32, "rect_meta"),
+                p(totals[2:], I32, "pool_head"), pool_cap, st), "sb_sort_tiles")
+            num_intersects, overflow, _ = (int(x) for x in totals.tolist())          # the one host read
+            if overflow:
+                rect_ids = rect_meta = None                 # deep tiles / many tiles per Gaussian: global path below
+            elif num_intersects < 1:
+                return empty_frame()
         final_ts = torch.empty(img_height, img_width, dtype=F32, device=dev)
         final_idx = torch.empty(img_height, img_width, dtype=I32, device=dev)
         out_alpha = torch.empty(img_height, img_width, dtype=F32, device=dev) if return_alpha else None
+        if rect_ids is None:
+            num_intersects, cum_tiles_hit = utils.compute_cumulative_intersects(num_tiles_hit)
+            if num_intersects < 1:
+                return empty_frame()
+            (_, _, _, gaussian_ids_sorted, tile_bins) = utils.bin_and_sort_gaussians(
+                n, num_intersects, xys_c, _f(depths), _f(radii), cum_tiles_hit, (tiles_x, tiles_y, 1),
+                block_width)
         # The kernels composite three channels per pass; other channel counts (upstream's nd_rasterize,
         # SURVEY.md 8f-4) run ceil(C/3) passes over the same sorted lists, zero-padding the last group.
-        groups = _channel_groups(channels)
-        parts, packs = [], []
-        for lo, width in groups:
-            cols_g, bg_g = _group3(colors, lo, width), _group3(background, lo, width)
-            packed = _pack(xys, conics, cols_g, opacity)
+        parts = []
+        if packs is None:
+            packs = [_pack(xys_c, conics_c, _group3(colors_c, lo, width), opacity_c) for lo, width in groups]
+        for gi, (lo, width) in enumerate(groups):
+            bg_g = _group3(background_c, lo, width)
             img_g = torch.empty(img_height, img_width, 3, dtype=F32, device=dev)
-            _abi.check(lib.sb_rasterize_fwd(
-                1, n, _abi.ptr(packed, F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
-                _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(bg_g, F32, "background"), img_height,
-                img_width, block_width, None, _abi.ptr(img_g, F32, "out_img"), _abi.ptr(final_ts, F32, "final_Ts"),
-                _abi.ptr(final_idx, I32, "final_idx"), _abi.ptr(out_alpha, F32, "out_alpha"), 0, None, 0, None,
-                _abi.stream()), "sb_rasterize_fwd")
+            if rect_ids is not None:
+                if gi > 0:
+                    work.zero_()              # the persistent kernel's queue head, consumed by the previous pass
+                _abi.check(lib.sb_rasterize_rect_fwd(
+                    1, n, p(packs[gi], F32, "packed"), p(rect_ids, I32, "rect_ids"), p(rect_meta, I32, "rect_meta"),
+                    p(bg_g, F32, "background"), img_height, img_width, None, p(img_g, F32, "out_img"),
+                    p(final_ts, F32, "final_Ts"), p(final_idx, I32, "final_idx"), p(out_alpha, F32, "out_alpha"), 0,
+                    None, 0, None, p(work, I32, "work_counter"), _abi.stream()), "sb_rasterize_rect_fwd")
+            else:
+                _abi.check(lib.sb_rasterize_fwd(
+                    1, n, p(packs[gi], F32, "packed"), p(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
+                    p(tile_bins, I32, "tile_bins"), p(bg_g, F32, "background"), img_height,
+                    img_width, block_width, None, p(img_g, F32, "out_img"), p(final_ts, F32, "final_Ts"),
+                    p(final_idx, I32, "final_idx"), p(out_alpha, F32, "out_alpha"), 0, None, 0, None,
+                    _abi.stream()), "sb_rasterize_fwd")
             parts.append(img_g if width == 3 else img_g[..., :width])
-            packs.append(packed)
         out_img = parts[0] if len(parts) == 1 else torch.cat(parts, dim=-1)
         ctx.empty = False
         ctx.num_intersects = num_intersects
+        ctx.rect = rect_ids is not None
         ctx.meta = (n, img_height, img_width, block_width, channels)
-        ctx.save_for_backward(gaussian_ids_sorted, tile_bins, background, final_ts, final_idx, conics, opacity,
-                              *packs)
+        lists = (rect_ids, rect_meta) if ctx.rect else (gaussian_ids_sorted, tile_bins)
+        ctx.save_for_backward(lists[0], lists[1], background_c, final_ts, final_idx, conics_c, opacity_c, *packs)
         ctx.set_materialize_grads(False)
         return (out_img, out_alpha) if return_alpha else out_img
 
@@ -216,8 +270,8 @@ class _RasterizeGaussians(Function):
         if ctx.empty or (v_out_img is None and v_out_alpha is None):
             return none12
         lib = _abi.load()
-        (gaussian_ids_sorted, tile_bins, background, final_ts, final_idx, conics, opacity,
-         *packs) = ctx.saved_tensors
+        p = _abi.ptr
+        (list_a, list_b, background, final_ts, final_idx, conics, opacity, *packs) = ctx.saved_tensors
         n, img_height, img_width, block_width, channels = ctx.meta
         dev = conics.device
         v_out_img = torch.zeros(img_height, img_width, channels, dtype=F32, device=dev) if v_out_img is None \
@@ -229,21 +283,29 @@ class _RasterizeGaussians(Function):
             v_img_g, bg_g = _group3(v_out_img, lo, width), _group3(background, lo, width)
             v_packed = torch.zeros(n, 12, dtype=F32, device=dev)
             # d/d alpha enters once: with the first group
-            _abi.check(lib.sb_rasterize_bwd(
-                1, n, _abi.ptr(packs[gi], F32, "packed"), _abi.ptr(gaussian_ids_sorted, I32, "gaussian_ids_sorted"),
-                _abi.ptr(tile_bins, I32, "tile_bins"), _abi.ptr(bg_g, F32, "background"), img_height,
-                img_width, block_width, _abi.ptr(final_ts, F32, "final_Ts"), _abi.ptr(final_idx, I32, "final_idx"),
-                _abi.ptr(v_img_g, F32, "v_out_img"), _abi.ptr(v_out_alpha if gi == 0 else None, F32, "v_out_alpha"),
-                None, 0, None, 0, None, _abi.ptr(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_bwd")
+            if ctx.rect:
+                _abi.check(lib.sb_rasterize_rect_bwd(
+                    1, n, p(packs[gi], F32, "packed"), p(list_a, I32, "rect_ids"), p(list_b, I32, "rect_meta"),
+                    p(bg_g, F32, "background"), img_height, img_width, p(final_ts, F32, "final_Ts"),
+                    p(final_idx, I32, "final_idx"), p(v_img_g, F32, "v_out_img"),
+                    p(v_out_alpha if gi == 0 else None, F32, "v_out_alpha"), None, 0, None, 0, None,
+                    p(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_rect_bwd")
+            else:
+                _abi.check(lib.sb_rasterize_bwd(
+                    1, n, p(packs[gi], F32, "packed"), p(list_a, I32, "gaussian_ids_sorted"),
+                    p(list_b, I32, "tile_bins"), p(bg_g, F32, "background"), img_height,
+                    img_width, block_width, p(final_ts, F32, "final_Ts"), p(final_idx, I32, "final_idx"),
+                    p(v_img_g, F32, "v_out_img"), p(v_out_alpha if gi == 0 else None, F32, "v_out_alpha"),
+                    None, 0, None, 0, None, p(v_packed, F32, "v_packed"), _abi.stream()), "sb_rasterize_bwd")
             g_xys = torch.empty(n, 2, dtype=F32, device=dev)
             g_conics = torch.empty(n, 3, dtype=F32, device=dev)
             g_colors = torch.empty(n, 3, dtype=F32, device=dev)
             g_opacity = torch.empty(n, 1, dtype=F32, device=dev)
             _abi.check(lib.sb_unpack_splat_grads(
-                n, _abi.ptr(v_packed, F32, "v_packed"), _abi.ptr(conics, F32, "conics"),
-                _abi.ptr(opacity, F32, "opacity"), _abi.ptr(g_xys, F32, "v_xys"),
-                _abi.ptr(g_conics, F32, "v_conics"), _abi.ptr(g_colors, F32, "v_colors"),
-                _abi.ptr(g_opacity, F32, "v_opacity"), _abi.stream()), "sb_unpack_splat_grads")
+                n, p(v_packed, F32, "v_packed"), p(conics, F32, "conics"),
+                p(opacity, F32, "opacity"), p(g_xys, F32, "v_xys"),
+                p(g_conics, F32, "v_conics"), p(g_colors, F32, "v_colors"),
+                p(g_opacity, F32, "v_opacity"), _abi.stream()), "sb_unpack_splat_grads")
             v_xys = g_xys if v_xys is None else v_xys + g_xys
             v_conics = g_conics if v_conics is None else v_conics + g_conics
             v_opacity = g_opacity if v_opacity is None else v_opacity + g_opacity

@@ -76,6 +76,34 @@ __global__ void __launch_bounds__(256) map_isect_kernel(
   }
 }
 
+// Binning of already projected Gaussians into the fixed-capacity tile segments of tile_sort.cu (what the fused
+// projection kernel does on the fly): one thread per (view, Gaussian) claims a slot in every tile of its bounding
+// box and drops (depth bits << 32 | id) there.  Lets gsplat.rasterize_gaussians -- which receives xys / depths /
+// radii from an earlier project_gaussians call -- use the per-tile sort and the rect-list rasterisers instead of
+// cumsum + host read + emission + 64-bit global sort + bin edges.
+__global__ void __launch_bounds__(256) bin_segments_kernel(int num_views, int n, const float* __restrict__ xys,
+                                                           int xy_stride, const float* __restrict__ depths,
+                                                           const int* __restrict__ radii, int tiles_x, int tiles_y,
+                                                           int bw, int* __restrict__ tile_counts,
+                                                           unsigned long long* __restrict__ tile_keys, int cap) {
+  const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= (size_t)num_views * n) return;
+  const int r = __ldg(radii + i);
+  if (r <= 0) return;
+  const int v = (int)(i / n), g = (int)(i - (size_t)v * n);
+  const float2 c = __ldg(reinterpret_cast<const float2*>(xys + i * xy_stride));
+  int min_x, max_x, min_y, max_y;
+  tile_bbox(c.x, c.y, (float)r, tiles_x, tiles_y, bw, min_x, max_x, min_y, max_y);
+  const unsigned long long key = ((unsigned long long)(unsigned)__float_as_int(__ldg(depths + i)) << 32) | (unsigned)g;
+  const size_t t0 = (size_t)v * tiles_x * tiles_y;
+  for (int ty = min_y; ty < max_y; ++ty)
+    for (int tx = min_x; tx < max_x; ++tx) {
+      const size_t t = t0 + (size_t)ty * tiles_x + tx;
+      const int pos = atomicAdd(tile_counts + t, 1);
+      if (pos < cap) tile_keys[t * cap + pos] = key;
+    }
+}
+
 // Depth pre-order of the fused path's global sort (tiles.cu: sb_depth_order_keys): key = view << 32 |
 // float32 bits of the depth (culled Gaussians: all ones in the low word -- they emit nothing, their place
 // does not matter), value = flat (view, Gaussian) index.
@@ -136,6 +164,20 @@ extern "C" int sb_map_gaussian_to_intersects(int num_views, int n, const float* 
   sb::map_isect_kernel<false><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       num_views, n, xys, xys_stride, depths, radii, cum_tiles_hit, tiles_x, tiles_y, block_width, isect_ids,
       gaussian_ids, nullptr);
+  SB_RETURN_LAST();
+}
+
+extern "C" int sb_bin_to_tile_segments(int num_views, int n, const float* xys, int xys_stride, const float* depths,
+                                       const int* radii, int tiles_x, int tiles_y, int block_width,
+                                       int* tile_counts, uint64_t* tile_keys, int tile_capacity, sb_stream_t stream) {
+  if (n < 0 || num_views < 1 || block_width < 2 || block_width > 16 || xys_stride < 2 || (xys_stride & 1) ||
+      !tile_counts || !tile_keys || tile_capacity < 1)
+    return SB_ERR_BAD_ARG;
+  const size_t total = (size_t)num_views * n;
+  if (total == 0) return 0;
+  sb::bin_segments_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      num_views, n, xys, xys_stride, depths, radii, tiles_x, tiles_y, block_width, tile_counts,
+      reinterpret_cast<unsigned long long*>(tile_keys), tile_capacity);
   SB_RETURN_LAST();
 }
 

@@ -217,6 +217,7 @@ def run_config3(args, steps, rank, world, dev, timed, V, H, W, n):
     import torch.distributed as dist
     from splatformer_b200 import dist as sbdist
     from splatformer_b200 import gs_utils, render, synth
+    from splatformer_b200.graphs import capture_step
     S = args.config3_scenes
     inv_views = 1.0 / V
     pix_step = S * V * H * W
@@ -248,6 +249,16 @@ def run_config3(args, steps, rank, world, dev, timed, V, H, W, n):
     ms, _, _, _ = timed(step_scene, steps)
     out["scene_sharded"] = {"value": pix_step / (ms / steps * 1e-3) / 1e6, "ms_per_step": ms / steps,
                             "scenes_per_rank": len(mine), "collective": "none"}
+    if args.graphs:
+        g, why = capture_step(step_scene, plan, len(mine))
+        if g is not None:
+            ms_g, _, _, _ = timed(lambda i: g.replay(), steps)
+            ok = plan.check()
+            out["scene_sharded"]["graph_replay"] = {"value": pix_step / (ms_g / steps * 1e-3) / 1e6,
+                                                    "ms_per_step": ms_g / steps, "no_overflow": ok}
+        else:
+            out["scene_sharded"]["graph_replay"] = {"unavailable": why}
+        del g
     del scenes
     if world == 1:
         out["view_sharded"] = None          # one GPU: the two layouts are the same loop
@@ -313,6 +324,18 @@ def run_config3(args, steps, rank, world, dev, timed, V, H, W, n):
     out["view_sharded"]["grad_rel_l2_vs_single_gpu"] = float(t.item())
     if float(t.item()) > 1e-4:
         raise SystemExit(f"view-sharded gradients differ from the single-GPU ones: rel L2 {float(t.item()):.3e}")
+    if args.graphs:
+        # the whole 8-scene step -- renders, backward passes and the 8 all-reduces, each forked onto NCCL's stream
+        # under the next scene's kernels and joined at the end -- as one CUDA graph: at 4 views per rank the eager
+        # loop is host-bound
+        g, why = capture_step(step_view(True, True), plan_v, S)
+        if g is not None:
+            ms_g, _, _, _ = timed(lambda i: g.replay(), steps)
+            ok = plan_v.check()
+            out["view_sharded"]["graph_replay"] = {"value": pix_step / (ms_g / steps * 1e-3) / 1e6,
+                                                   "ms_per_step": ms_g / steps, "no_overflow": ok}
+        else:
+            out["view_sharded"]["graph_replay"] = {"unavailable": why}
     return out
 
 
@@ -391,6 +414,8 @@ def main() -> None:
     ap.add_argument("--config3-steps", type=int, default=None,
                     help="timed steps of the 8-scene train-step shape (default: steps // 5, at least 4; 0 = skip)")
     ap.add_argument("--config3-scenes", type=int, default=8)
+    ap.add_argument("--graphs", type=int, default=1,
+                    help="1: also time config 3's step replayed from one captured CUDA graph; 0: skip")
     ap.add_argument("--other-configs", type=int, default=1,
                     help="1: also time BASELINE configs 4 and 5 (single GPU) after the headline; 0: skip")
     ap.add_argument("--ref-views", type=int, default=2)

@@ -114,10 +114,18 @@ class _Totals:
         self.host, self.event, self.key, self.plan, self.value, self.folded = host, event, key, plan, value, False
 
     def ready(self) -> bool:
-        return self.value is not None or self.event.query()
+        return self.value is not None or (self.event is not None and self.event.query())
 
     def read(self) -> Tuple[int, int, int]:
-        """(intersections, overflow flags, rect-list entries); waits for the device to have produced them."""
+        """(intersections, overflow flags, rect-list entries); waits for the device to have produced them.
+        A pass enqueued under a graph-safe plan carries no event (none may be waited for inside a captured
+        region): its totals are read after a stream synchronisation and are not cached -- every replay of the
+        graph rewrites the slot."""
+        if self.event is None and self.host is not None:
+            torch.cuda.current_stream().synchronize()
+            vals = (int(self.host[0]), int(self.host[1]), int(self.host[2]))
+            self.plan._fold(self.key, *vals)
+            return vals
         if self.value is None:
             self.event.synchronize()
             self.value = (int(self.host[0]), int(self.host[1]), int(self.host[2]))
@@ -135,6 +143,13 @@ class RenderPlan:
 
     def __init__(self, tile_capacity: Optional[int] = None):
         self.tile_capacity = tile_capacity
+        # graph_safe: enqueue passes with nothing a CUDA graph capture could not hold -- no event that the host
+        # waits for, no flag read in the backward, no replay.  For call sites that capture whole steps
+        # (torch.cuda.graph) after an eager warm-up has taught the plan its shapes; `check()` after a replay
+        # tells whether any captured pass overflowed (then the step has to be redone eagerly).
+        self.graph_safe = False
+        self.graph_totals: List[_Totals] = []
+        self._graph_slot_pool: List[Tensor] = []
         self.overflowed: Dict[Tuple[int, int, int], int] = {}
         self.prefer_global: Dict[Tuple[int, int, int], bool] = {}
         self.pending: List[_Totals] = []
@@ -188,6 +203,25 @@ class RenderPlan:
         used = self.pool_used.get(key)
         want = int(used * 1.3) + (1 << 20) if used else max(12 * v * n, 1 << 20)
         return max(1024, min(ceiling, (want + (1 << 20) - 1) >> 20 << 20))
+
+    def reserve_graph_slots(self, count: int) -> None:
+        """Pinned landing buffers for `count` passes about to be captured (pinned memory cannot be allocated
+        while a stream is capturing)."""
+        while len(self._graph_slot_pool) < count:
+            self._graph_slot_pool.append(torch.zeros(3, dtype=I32).pin_memory())
+
+    def graph_slot(self) -> Tensor:
+        if not self._graph_slot_pool:
+            self.reserve_graph_slots(1)          # (raises under capture: call reserve_graph_slots before)
+        return self._graph_slot_pool.pop()
+
+    def check(self) -> bool:
+        """Graph-safe plans: True if no pass enqueued (captured) through this plan overflowed in its latest
+        execution.  Synchronises the stream."""
+        ok = True
+        for t in self.graph_totals:
+            ok = ok and t.read()[1] == 0
+        return ok
 
     def poll(self) -> None:
         """Fold in the totals of earlier calls that have reached the host by now (never blocks)."""
@@ -375,7 +409,14 @@ class _Pass:
             ready = torch.cuda.Event()
             ready.record()
             return _Totals(host_totals, ready, (v, num_tiles, self.n), plan)
-        result = plan.host_slot(landed)
+        if plan.graph_safe:
+            # a slot of its own (a captured copy keeps writing to it on every replay), no event
+            slot = plan.graph_slot()
+            slot.copy_(totals, non_blocking=True)
+            result = _Totals(slot, None, (v, num_tiles, self.n), plan)
+            plan.graph_totals.append(result)
+        else:
+            result = plan.host_slot(landed)
         # the raster kernel is enqueued optimistically: the device produced the flag BEFORE it starts
         if use_rect:
             self.raster_rect(view_has, work)
@@ -471,7 +512,9 @@ class _RenderViews(Function):
                 key = (v, ps.num_tiles, n)
                 first = key not in plan.seen
                 plan.seen.add(key)
-                if not training or first:
+                if plan.graph_safe:
+                    pass                    # nothing may be read here: plan.check() after the (replayed) step
+                elif not training or first:
                     # evaluation (nothing will come back to repair an overflowed pass) or a shape this plan has
                     # not seen yet: look right away
                     if totals.read()[1]:
@@ -531,7 +574,7 @@ class _RenderViews(Function):
             st = _abi.stream()
             ps.st = st
             # the binning flag of the forward: the device wrote it before the forward rasteriser started
-            num_intersects, overflow, _ = ctx.totals.read()
+            overflow = 0 if ctx.plan.graph_safe else ctx.totals.read()[1]
             if overflow:
                 # a tile ran over its segment: the lists the forward walked were truncated.  Redo the pass with
                 # the global sort over the same buffers (images and loss sums are corrected in place), then

@@ -315,27 +315,28 @@ def run_config3(args, steps, rank, world, dev, timed, V, H, W, n):
     full_raw, full_cams, full_gt = load(0, 0, V)
     l1f, _ = gs_utils.render_l1_loss(full_raw, full_cams, full_gt)
     (l1f.sum() * inv_views).backward()
-    worst = 0.0
+    per = {}
     for k in raw:
         a, b = raw[k].grad.double(), full_raw[k].grad.double()
-        worst = max(worst, float((a - b).norm() / b.norm().clamp_min(1e-30)))
+        finite = bool(torch.isfinite(a).all()) and bool(torch.isfinite(b).all())
+        per[k] = float((a - b).norm() / b.norm().clamp_min(1e-30)) if finite else float("inf")
+    worst = max(per.values())
     t = torch.tensor([worst], device=dev, dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    out["view_sharded"]["grad_rel_l2_vs_single_gpu"] = float(t.item())
-    if float(t.item()) > 1e-4:
-        raise SystemExit(f"view-sharded gradients differ from the single-GPU ones: rel L2 {float(t.item()):.3e}")
+    worst = float(t.item())
+    out["view_sharded"]["grad_rel_l2_vs_single_gpu"] = worst
+    out["view_sharded"]["grad_rel_l2_per_tensor"] = per
+    if not (worst <= 1e-4):          # also true for NaN / inf
+        raise SystemExit(f"view-sharded gradients differ from the single-GPU ones: rel L2 {worst:.3e} ({per})")
     if args.graphs:
-        # the whole 8-scene step -- renders, backward passes and the 8 all-reduces, each forked onto NCCL's stream
-        # under the next scene's kernels and joined at the end -- as one CUDA graph: at 4 views per rank the eager
-        # loop is host-bound
-        g, why = capture_step(step_view(True, True), plan_v, S)
-        if g is not None:
-            ms_g, _, _, _ = timed(lambda i: g.replay(), steps)
-            ok = plan_v.check()
-            out["view_sharded"]["graph_replay"] = {"value": pix_step / (ms_g / steps * 1e-3) / 1e6,
-                                                   "ms_per_step": ms_g / steps, "no_overflow": ok}
-        else:
-            out["view_sharded"]["graph_replay"] = {"unavailable": why}
+        # Not attempted: an NCCL all-reduce issued while the stream is being captured invalidates the capture
+        # (cudaErrorStreamCaptureInvalidated) with the async work handle, and the blocking form hung a 2-rank
+        # capture on this stack (torch 2.11 / NCCL 2.28.9) until the box's limit.  The scene-sharded step, which
+        # has no collective, is captured above; the view-sharded step's renders alone capture and replay
+        # correctly (2 ranks, round 2: gradients within 2e-6 rel. of the eager step, no overflow).
+        out["view_sharded"]["graph_replay"] = {
+            "unavailable": "NCCL all-reduce inside stream capture invalidates the capture (async handle) or hangs "
+                           "(blocking) on this stack; not attempted, the scene-sharded step is the captured one"}
     return out
 
 

@@ -4,13 +4,15 @@
 // (/root/reference/utils/gs_utils.py:96-109), the uint32 tile-index sort of the fused path's global-sort
 // branch, and compute_cumulative_intersects' cumsum.  No library calls: three kernels.
 //
-//   digit_histogram_kernel   one read of the keys: 256-bin histograms of EVERY pass's digit (warp-aggregated
-//                            shared-memory counts, one global atomic per bin and CTA).
+//   digit_histogram_kernel   one read of the keys: 256-bin histograms of EVERY pass's digit (every thread run-length
+//                            encodes 16 consecutive keys, one shared atomic per run, one global atomic per bin and CTA).
 //   onesweep_kernel          one pass = one read + one write of the pairs.  A CTA takes the next tile of
 //                            512 x IPT consecutive pairs (dynamic tile index, so that every predecessor of a
 //                            running tile is running or done), ranks them stably by the pass's 8-bit digit
-//                            (per warp: MATCH.ANY on the digit, the lowest matching lane bumps the warp's
-//                            digit counter; per CTA: a scan of the 16 warps' counters), publishes its 256
+//                            (per warp: every lane ORs its bit into the digit's word of a shared bitmap --
+//                            ATOMS.OR, not MATCH.ANY, which costs ~60 cycles per warp on the SM's one ADU --
+//                            and ranks itself by popc below its lane; the warp's digit counter grows by the
+//                            word's popc; per CTA: a scan of the 16 warps' counters), publishes its 256
 //                            digit counts, looks back over the preceding tiles' counts / inclusive prefixes
 //                            (one thread per digit, flag in the top two bits of a 32-bit word), and scatters
 //                            through shared memory so that the stores leave in digit-contiguous runs.

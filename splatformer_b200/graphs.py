@@ -3,8 +3,10 @@
 The fused path enqueues five kernels and two memsets per scene step plus a handful of small torch kernels; when a
 step is short (few views per rank, small scenes) or the host is contended (eight ranks on one box), the Python and
 launch cost per pass (about 0.55 ms, scripts/host_overhead.py) is what bounds the loop, not the device.  Capturing
-the step -- forward and backward of every scene it renders, the all-reduces of view-sharded scenes included -- into
-ONE CUDA graph makes a step cost the host a single launch.
+the step -- forward and backward of every scene it renders -- into ONE CUDA graph makes a step cost the host a
+single launch.  Collectives stay outside: an NCCL all-reduce issued while the stream captures invalidates the capture
+(async work handle) or hangs (blocking form) on this stack (torch 2.11, NCCL 2.28.9), so a view-sharded step captures
+its renders and issues `dist.sync_gaussian_grads`' reduces eagerly between replays, or is not captured at all.
 
 What a captured region must not contain -- an event the host waits for, a flag read, a replay decision -- is exactly
 what `RenderPlan.graph_safe` switches off.  So the recipe is: run the step eagerly a few times (the plan learns the
@@ -39,7 +41,7 @@ def capture_step(step_fn: Callable[[int], None], plan: RenderPlan, passes: int
         torch.cuda.synchronize()
         plan.graph_totals.clear()
         graph = torch.cuda.CUDAGraph()
-        # thread_local: other threads of the process (NCCL's watchdog polls events) may keep calling the runtime
+        # thread_local: other threads of the process (a data loader, NCCL's watchdog) may keep calling the runtime
         with torch.cuda.graph(graph, capture_error_mode="thread_local"):
             step_fn(0)
         return graph, None

@@ -36,6 +36,7 @@ extern "C" {
 #define SB_ABI_VERSION 3
 #define SB_ERR_BAD_ARG (-1)
 #define SB_ERR_TEMP_TOO_SMALL (-2)
+#define SB_ERR_STATIC_SCRATCH_EXCEEDED (-3) /* sb_cumsum_i32_static: count > SB_CUMSUM_STATIC_MAX_COUNT */
 
 typedef void* sb_stream_t; /* cudaStream_t */
 
@@ -89,6 +90,24 @@ SB_API int sb_project_bwd(int num_views, int n, const float* means, const float*
 SB_API size_t sb_cumsum_temp_bytes(int count);
 SB_API int sb_cumsum_i32(int count, const int* in, int* out, void* temp, size_t temp_bytes,
                   sb_stream_t stream);
+/* The same prefix sum for callers that may not allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The look-back state lives in a file-scope
+ * `static __device__` array of the library (64 + 8 * SB_CUMSUM_STATIC_MAX_COUNT / 4096 =
+ * 32 832 bytes, held by every GPU that loads the library until the process exits) -- the one
+ * exception to "no global mutable state" above.  The call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine); the caller still passes `in` and `out`.
+ *  - count > SB_CUMSUM_STATIC_MAX_COUNT returns SB_ERR_STATIC_SCRATCH_EXCEEDED before any
+ *    CUDA call; count < 0 or a NULL pointer returns SB_ERR_BAD_ARG; count == 0 is a no-op.
+ *  - the array is shared by every call on a device and keeps the previous call's contents:
+ *    each call clears, on `stream`, the counter and the status words it is going to use.
+ *    Calls that overlap on the GPU (streams with no ordering between them) RACE on it:
+ *    serialise them.
+ *  - the array's device address is looked up once per device (cudaGetSymbolAddress with that
+ *    device current): make the first call on a device outside a stream capture.
+ * Output identical to sb_cumsum_i32 (integer arithmetic, bit-exact). */
+#define SB_CUMSUM_STATIC_MAX_COUNT (1 << 24)
+SB_API int sb_cumsum_i32_static(int count, const int* in, int* out, sb_stream_t stream);
 
 /* ---- a6: gsplat.utils.map_gaussian_to_intersects (_C.map_gaussian_to_intersects) -------
  * key = ((view*T + tile) << 32) | float32 bits of depth; gaussian_ids are view-local.

@@ -23,6 +23,8 @@ ABI_VERSION = 3
 FLAG_RAW_SCALES, FLAG_RAW_OPACITIES, FLAG_COLOR_SIGMOID, FLAG_C2W_OPENGL = 1, 2, 4, 8
 FLAG_INTRINS_SHARED = 16            # intrins is (1,4), shared by all views
 FLAG_RAW_QUATS = 32                 # quats are raw: wrapper's q / |q| and (0,0,0,1) substitution in-kernel
+ERR_BAD_ARG, ERR_TEMP_TOO_SMALL, ERR_STATIC_SCRATCH_EXCEEDED = -1, -2, -3
+CUMSUM_STATIC_MAX_COUNT = 1 << 24   # sb_cumsum_i32_static: elements its file-scope device scratch covers
 
 # name -> (restype, argtypes); mirrors include/splat_b200.h one to one
 SIGNATURES = {
@@ -34,6 +36,7 @@ SIGNATURES = {
     "sb_project_bwd": (I, [I, I, P, P, F, P, P, I, P, F, F, F, F, I, I, I, F, P, P, P, P, P, P, P, P, P, P, P]),
     "sb_cumsum_temp_bytes": (S, [I]),
     "sb_cumsum_i32": (I, [I, P, P, P, S, P]),
+    "sb_cumsum_i32_static": (I, [I, P, P, P]),
     "sb_map_gaussian_to_intersects": (I, [I, I, P, I, P, P, P, I, I, I, P, P, P]),
     "sb_depth_order_keys": (I, [I, I, P, P, P, P, P]),
     "sb_gather_i32": (I, [I, P, P, P, P]),

@@ -76,6 +76,9 @@ extern "C" int sb_abi_version(void) { return SB_ABI_VERSION; }
 extern "C" const char* sb_error_string(int code) {
   if (code == SB_ERR_BAD_ARG) return "splat_b200: invalid argument";
   if (code == SB_ERR_TEMP_TOO_SMALL) return "splat_b200: scratch buffer too small";
+  if (code == SB_ERR_STATIC_SCRATCH_EXCEEDED)
+    return "splat_b200: count exceeds the static scratch of the no-allocation entry point "
+           "(SB_CUMSUM_STATIC_MAX_COUNT = 16777216 elements); use sb_cumsum_i32 with a caller-supplied buffer";
   return cudaGetErrorString((cudaError_t)code);
 }
 

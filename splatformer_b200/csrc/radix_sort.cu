@@ -616,3 +616,63 @@ extern "C" int sb_sort_tiles_global(int count, int num_tiles_total, const uint32
                                                                                 reinterpret_cast<int2*>(tile_bins));
   SB_RETURN_LAST();
 }
+
+// ---- the prefix sum for callers that may not allocate ---------------------------------------------------------
+// sb_cumsum_i32_static: sb_cumsum_i32 with the look-back state in a file-scope device array instead of a buffer
+// the caller allocates (code under CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No
+// counterpart in the reference.  The array is part of the library's
+// image: every GPU that loads the library holds its 32 832 bytes until the process exits.  It is shared by every
+// call on a device and keeps the last call's contents, so (a) the tile counter and the status words the call is
+// going to use are cleared on the call's stream before the kernel, (b) two calls that overlap on the GPU (different
+// streams without an ordering between them) race on it -- callers serialise.  Nothing here calls cudaMalloc /
+// cudaFree or a routine that does; cudaGetSymbolAddress runs once per device (the first call on that device, which
+// should therefore be made outside a stream capture).
+namespace sb {
+
+constexpr int kStaticScanMaxCount = SB_CUMSUM_STATIC_MAX_COUNT;
+static_assert(kStaticScanMaxCount % kScanTile == 0, "whole tiles");
+constexpr int kStaticScanMaxTiles = kStaticScanMaxCount / kScanTile;
+constexpr size_t kStaticScanBytes = 64 + (size_t)kStaticScanMaxTiles * 8;        // [counter (64 B) | status words]
+static __device__ __align__(256) unsigned char g_static_scan_scratch[kStaticScanBytes];
+
+// In host code `g_static_scan_scratch` is a host-side stand-in for the symbol, not a device address: the kernel
+// gets the address cudaGetSymbolAddress reports for the CURRENT device, looked up once per device.
+constexpr int kMaxDevices = 64;
+static unsigned char* volatile g_static_scan_ptr[kMaxDevices];                    // zero-initialised; same value from any thread
+
+static int static_scan_scratch(unsigned char** out) {
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return (int)err;
+  if (dev < 0 || dev >= kMaxDevices) return SB_ERR_BAD_ARG;
+  unsigned char* p = g_static_scan_ptr[dev];
+  if (!p) {
+    void* sym = nullptr;
+    err = cudaGetSymbolAddress(&sym, g_static_scan_scratch);
+    if (err != cudaSuccess) return (int)err;
+    if (!sym) return (int)cudaErrorInvalidSymbol;
+    p = reinterpret_cast<unsigned char*>(sym);
+    g_static_scan_ptr[dev] = p;
+  }
+  *out = p;
+  return 0;
+}
+
+}  // namespace sb
+
+extern "C" int sb_cumsum_i32_static(int count, const int* in, int* out, sb_stream_t stream) {
+  if (count < 0) return SB_ERR_BAD_ARG;
+  if (count > sb::kStaticScanMaxCount) return SB_ERR_STATIC_SCRATCH_EXCEEDED;   // before any CUDA call
+  if (count == 0) return 0;
+  if (!in || !out) return SB_ERR_BAD_ARG;
+  unsigned char* base = nullptr;
+  const int rc = sb::static_scan_scratch(&base);
+  if (rc != 0) return rc;
+  const unsigned tiles = (unsigned)(((size_t)count + sb::kScanTile - 1) / sb::kScanTile);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t err = cudaMemsetAsync(base, 0, 64 + (size_t)tiles * 8, st);        // what must start at zero
+  if (err != cudaSuccess) return (int)err;
+  sb::scan_kernel<<<tiles, sb::kScanThreads, 0, st>>>(in, out, count, reinterpret_cast<unsigned long long*>(base + 64),
+                                                      reinterpret_cast<unsigned*>(base));
+  SB_RETURN_LAST();
+}

@@ -95,6 +95,33 @@ __device__ __forceinline__ int grab_rect(int* work, int lane) {
   if (lane == 0) r = atomicAdd(work, 1);
   return __shfl_sync(0xffffffffu, r, 0);
 }
+// the same in two halves: the atomic is issued where the number is wanted EARLY, the broadcast (which waits for the
+// atomic's round trip to L2) where it is needed
+// `opaque_zero` is a lane's value that is 0 at run time but that ptxas cannot prove to be: with a provably uniform
+// address ptxas wraps the atomic in its warp-aggregation pattern (VOTE / elect / ATOMG / SHFL), and that SHFL waits
+// for the atomic on the spot (ncu source page: 5 % of the kernel's samples).
+__device__ __forceinline__ int grab_rect_issue(int* work, int lane, int opaque_zero) {
+  int r = 0;
+  if (lane == 0) asm volatile("atom.global.add.u32 %0, [%1], 1;" : "=r"(r) : "l"(work + opaque_zero) : "memory");
+  return r;
+}
+
+// One record of the forward walk: centre (rA.xy), conic + log2 opacity (rB), colour (rC.xyz).  rC.w (the opacity)
+// is not needed here but is STORED with the rest (stage_pair_slots_fwd): a dead component of a vector load is a
+// register ptxas hands to the next temporary, and the write to it then waits for the load (write-after-write on the
+// load's destination) -- the whole gather latency, in front of the walk that was meant to hide it (ncu source page:
+// 9 % of the kernel's samples on one LOP3).  Splitting the load does not help: ptxas fuses the pieces again.
+__device__ __forceinline__ void load_record_fwd(const float4* __restrict__ p, float4& rA, float4& rB, float4& rC) {
+  const float2 c = __ldg(reinterpret_cast<const float2*>(p));
+  rA.x = c.x; rA.y = c.y;
+  rB = __ldg(p + 1);
+  rC = __ldg(p + 2);
+}
+__device__ __forceinline__ void stage_pair_slots_fwd(PairSlots& sl, int lane, const float4& rA, const float4& rB,
+                                                     const float4& rC) {
+  stage_pair_slots(sl, lane, rA, rB, rC);
+  reinterpret_cast<float*>(sl.q4 + (lane >> 1))[2 + (lane & 1)] = rC.w;       // keeps rC.w live until here
+}
 
 __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect_fwd_kernel(
     int n, const float4* __restrict__ packed, const int* __restrict__ rect_ids,
@@ -128,16 +155,18 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
   float4 rA = nullA, rB = nullB, rC = nullA;
   if (lane < meta0.y) {
     const int v0 = (r0 >> 3) / tiles;
-    const float4* p = packed + ((size_t)v0 * n + __ldg(rect_ids + meta0.x + lane)) * 3;
-    rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
+    load_record_fwd(packed + ((size_t)v0 * n + __ldg(rect_ids + meta0.x + lane)) * 3, rA, rB, rC);
   }
 
   while (true) {
     // ---- lookahead loads: ids of k+2, (start, count) of k+3, counter fetch for k+4 ----
     const int id2 = lane < meta2.y ? __ldg(rect_ids + meta2.x + lane) : 0;
     const int2 meta3 = r3 < total_rects ? __ldg(rect_meta + r3) : none;
-    const int r4 = grab_rect(work, lane);
+    const int r4_lane0 = grab_rect_issue(work, lane, (int)((unsigned)(meta1.y | id1) >> 31));      // broadcast at the bottom of the rectangle
     const int count1 = meta1.y;
+    // ids of this rectangle's SECOND chunk: the records of chunk c + 1 are requested at the top of chunk c, so
+    // their ids must be in registers by then -- one chunk ahead of the records, two ahead of the walk
+    int idn = 32 + lane < meta0.y ? __ldg(rect_ids + meta0.x + 32 + lane) : 0;
 
     const int tg = r0 >> 3, wt = r0 & 7;
     const int v = tg / tiles, tile = tg - v * tiles;
@@ -145,6 +174,8 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
     const RectGeom rg = rect_geom(tile_x, tile_y, wt, lane, img_w, img_h);
     const int count = meta0.y;
     const int* ids = rect_ids + meta0.x;
+    // the loss epilogue's target pixel: its load sat exposed at the end of every rectangle (5 % of the samples)
+    if (gt && rg.inside && count > 0) prefetch_gt(gt, gt_u8, ((size_t)v * img_h + rg.py_i) * img_w + rg.px_i);
     const float4* vp = packed + (size_t)v * n * 3;
     const float4* vp1 = packed + (size_t)((r1 >> 3) / tiles) * n * 3;      // only used when r1 is valid
 
@@ -157,21 +188,16 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
 
     for (int c0 = 0; c0 < count; c0 += 32) {
       __syncwarp();
-      stage_pair_slots(sl, lane, rA, rB, rC);
+      stage_pair_slots_fwd(sl, lane, rA, rB, rC);
       __syncwarp();
       rB = nullB;
       if (c0 + 32 < count) {
-        if (c0 + 32 + lane < count) {
-          const float4* p = vp + (size_t)__ldg(ids + c0 + 32 + lane) * 3;
-          rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
-        }
+        if (c0 + 32 + lane < count) load_record_fwd(vp + (size_t)idn * 3, rA, rB, rC);
+        if (c0 + 64 + lane < count) idn = __ldg(ids + c0 + 64 + lane);
       } else {
         // last chunk of this rectangle: the registers now take the first chunk of the next one
         fetched_next = true;
-        if (lane < count1) {
-          const float4* p = vp1 + (size_t)id1 * 3;
-          rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
-        }
+        if (lane < count1) load_record_fwd(vp1 + (size_t)id1 * 3, rA, rB, rC);
       }
       const int npairs = (min(32, count - c0) + 1) >> 1;
       SB_UNROLL_(SB_RECT_FWD_UNROLL)
@@ -218,10 +244,7 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
     if (!fetched_next) {
       // empty list, or every pixel saturated before the last chunk
       rB = nullB;
-      if (lane < count1) {
-        const float4* p = vp1 + (size_t)id1 * 3;
-        rA = __ldg(p); rB = __ldg(p + 1); rC = __ldg(p + 2);
-      }
+      if (lane < count1) load_record_fwd(vp1 + (size_t)id1 * 3, rA, rB, rC);
     }
 
     float pr, pg;
@@ -257,6 +280,7 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
       if (lane == 0) *reinterpret_cast<float2*>(loss_partial + (size_t)r0 * 2) = make_float2(l1, l2);
     }
 
+    const int r4 = __shfl_sync(0xffffffffu, r4_lane0, 0);
     if (r1 >= total_rects) break;
     r0 = r1; meta0 = meta1;
     r1 = r2; meta1 = meta2; id1 = id2;

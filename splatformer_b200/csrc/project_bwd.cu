@@ -205,20 +205,29 @@ __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_projec
       // ---- scan: record (view vc0 + p / 8, row p % 8); per row, the views whose record is not all-zero ----
       int cnt = 0;
       const int total = vc * kBwdRowsPerWarp;
-      for (int p0 = 0; p0 < total; p0 += 32) {
-        const int p = p0 + lane;
-        const int vv = p >> 3;
-        bool nz = false;
-        if (p < total && scan_r < rows_w) {
-          const float4* rec = v_packed + 3 * ((size_t)(vc0 + vv) * n + g0 + row0 + scan_r);
-          const float4 a = __ldg(rec), b = __ldg(rec + 1);
-          const float c = __ldg(reinterpret_cast<const float*>(rec + 2));
-          nz = a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f || b.x != 0.f || b.y != 0.f || b.z != 0.f ||
-               b.w != 0.f || c != 0.f;
+      // two steps' records are requested before the first is looked at: a step's ballot depends on its loads, so a
+      // plain loop exposed one memory round trip per 32 records (ncu source page: 16 % of the kernel's samples on
+      // the first compare).  "Not all-zero" is taken on the bits (a -0.0 counts as set: such a pair is walked
+      // and adds zeros).
+      for (int p0 = 0; p0 < total; p0 += 64) {
+        unsigned bits[2] = {0u, 0u};
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int p = p0 + 32 * u + lane;
+          if (p < total && scan_r < rows_w) {
+            const uint4* rec = reinterpret_cast<const uint4*>(v_packed + 3 * ((size_t)(vc0 + (p >> 3)) * n + g0 + row0 + scan_r));
+            const uint4 a = __ldg(rec), b = __ldg(rec + 1);
+            const unsigned c = __ldg(reinterpret_cast<const unsigned*>(rec + 2));
+            bits[u] = a.x | a.y | a.z | a.w | b.x | b.y | b.z | b.w | c;
+          }
         }
-        const unsigned bal = __ballot_sync(0xffffffffu, nz) & row_mask;
-        if (nz) s_list[(row0 + scan_r) * kBwdViewChunk + cnt + __popc(bal & lt)] = (unsigned char)vv;
-        cnt += __popc(bal);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const bool nz = (bits[u] << 1) != 0u;            // the sign bit alone is -0.0
+          const unsigned bal = __ballot_sync(0xffffffffu, nz) & row_mask;
+          if (nz) s_list[(row0 + scan_r) * kBwdViewChunk + cnt + __popc(bal & lt)] = (unsigned char)((p0 + 32 * u + lane) >> 3);
+          cnt += __popc(bal);
+        }
       }
       if (lane < kBwdRowsPerWarp) s_cnt[row0 + lane] = cnt;
       n_scanned += (lane < rows_w) ? vc : 0;
@@ -237,13 +246,16 @@ __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_projec
           cam = load_cam(cams, v);
           cam_limits(cam, img_w, img_h, lim_x, lim_y);
         }
-        ProjFwd f;
-        project_fwd_view(m, sg, cam, lim_x, lim_y, img_w, img_h, bw, clip, f);
-        if (!f.valid) continue;                        // (a culled pair's record is never written: not reached)
+        // the pair's gradient record and colour row are requested BEFORE the projection is recomputed (its ~150
+        // dependent instructions are what hides them; behind it the first use waited a whole round trip: 15 % of
+        // the kernel's samples)
         const size_t i = (size_t)v * n + gl;
         const float4 ga = __ldg(v_packed + 3 * i), gb = __ldg(v_packed + 3 * i + 1);
         const float gcx = __ldg(reinterpret_cast<const float*>(v_packed + 3 * i + 2));
         const float4 col = __ldg(packed + 3 * i + 2);       // r, g, b (after the clamp), opacity
+        ProjFwd f;
+        project_fwd_view(m, sg, cam, lim_x, lim_y, img_w, img_h, bw, clip, f);
+        if (!f.valid) continue;                        // (a culled pair's record is never written: not reached)
         op = col.w; col0 = col.x; col1 = col.y; col2 = col.z;
         float vm[3], G[9];
         float vx, vy, vca, vcb, vcc, vop;

@@ -417,6 +417,9 @@ def main() -> None:
     ap.add_argument("--config3-scenes", type=int, default=8)
     ap.add_argument("--graphs", type=int, default=1,
                     help="1: also time config 3's step replayed from one captured CUDA graph; 0: skip")
+    ap.add_argument("--headline", choices=["graph", "eager"], default="graph",
+                    help="graph: value / e2e are the step replayed from a captured CUDA graph when the capture "
+                         "succeeds (the eager loop is reported under `eager`); eager: the uncaptured calls")
     ap.add_argument("--other-configs", type=int, default=1,
                     help="1: also time BASELINE configs 4 and 5 (single GPU) after the headline; 0: skip")
     ap.add_argument("--ref-views", type=int, default=2)
@@ -480,6 +483,8 @@ def main() -> None:
     h2d_bytes = sum(v.numel() * v.element_size() for v in host[0][0].values()) \
         + sum(v.numel() * v.element_size() for v in host[0][1].values()) \
         + host[0][2].numel() * host[0][2].element_size()
+
+    host_scenes = list(host)              # (tensor by tensor; `host` may be re-packed for --e2e-packed below)
 
     def render_loss(raw, cams, gt):
         # train.py:272-275 in one public call: per-view mean |pred - gt| of all views of the scene
@@ -584,6 +589,105 @@ def main() -> None:
     ms_total, launches, stage_ms, stage_calls = timed(step_resident, args.steps, with_stages=True)
     isect_per_view = render.last_num_intersects() / max(v_local, 1)
 
+    # ---- the same step replayed from a CUDA graph (splatformer_b200.graphs.capture_step): one graph per resident
+    # scene, replayed in the same rotation; what a training loop that captures its render step runs ----
+    graph_replay = None
+    if args.graphs and not (args.shard == "view" and world > 1):
+        from splatformer_b200.graphs import capture_step
+        plans = [render.RenderPlan() for _ in range(NSCENE)]
+
+        graphs, why = [], None
+        graph_loss = [None] * NSCENE
+
+        def scene_step_keep_loss(sidx):
+            def fn(i):
+                raw, cams, gt = resident[sidx]
+                for p in raw.values():
+                    p.grad = None
+                l1, _ = gs_utils.render_l1_loss(raw, cams, gt, plan=plans[sidx])
+                loss = l1.sum() * inv_views
+                loss.backward()
+                graph_loss[sidx] = loss.detach()          # static: the graph rewrites it on every replay
+            return fn
+        for sidx in range(NSCENE):
+            fn = scene_step_keep_loss(sidx)
+            for _ in range(2):
+                fn(0)
+            g, why = capture_step(fn, plans[sidx], 1)
+            if g is None:
+                break
+            graphs.append(g)
+        if len(graphs) == NSCENE:
+            for i in range(3):
+                graphs[i % NSCENE].replay()
+            ms_g, _, _, _ = timed(lambda i: graphs[i % NSCENE].replay(), args.steps)
+            graph_replay = {"ms_per_step": ms_g / args.steps, "no_overflow": all(p.check() for p in plans),
+                            "api": "splatformer_b200.graphs.capture_step(step, plan, passes=1): forward + backward "
+                                   "of one scene as one CUDA graph per resident scene, same rotation"}
+            if not args.no_e2e:
+                # end to end through the graphs: every step's scene is copied from pinned host memory INTO the
+                # captured input tensors of the graph that will run one step later (copy stream, overlapped with
+                # the running replay), the loss is read from pinned memory one step later -- the same bytes and the
+                # same reads as the eager e2e loop below
+                copy_stream = torch.cuda.Stream()
+                uploaded = [torch.cuda.Event() for _ in range(NSCENE)]
+                consumed = [torch.cuda.Event() for _ in range(NSCENE)]
+                ge = {"steps": 0, "pending": [], "losses": []}
+                ring = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(4)]
+
+                def upload(sidx):
+                    gs_h, cams_h, gt_h = host_scenes[sidx]
+                    raw, cams, gt = resident[sidx]
+                    with torch.cuda.stream(copy_stream):
+                        copy_stream.wait_event(consumed[sidx])
+                        for k, v in gs_h.items():
+                            raw[k].data.copy_(v, non_blocking=True)
+                        for k, v in cams_h.items():
+                            cams[k].copy_(v, non_blocking=True)
+                        gt.copy_(gt_h, non_blocking=True)
+                        uploaded[sidx].record(copy_stream)
+
+                def step_e2e_graph(i):
+                    sidx = i % NSCENE
+                    if i == 0:
+                        upload(0)
+                    cur = torch.cuda.current_stream()
+                    cur.wait_event(uploaded[sidx])
+                    graphs[sidx].replay()
+                    consumed[sidx].record(cur)
+                    if i + 1 < ge["steps"]:
+                        upload((i + 1) % NSCENE)
+                    slot = ring[i % len(ring)]
+                    slot.copy_(graph_loss[sidx].reshape(1), non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record()
+                    ge["pending"].append((ev, slot))
+                    if len(ge["pending"]) > 1:
+                        ev0, s0 = ge["pending"].pop(0)
+                        ev0.synchronize()
+                        ge["losses"].append(float(s0[0]))
+
+                def drain():
+                    while ge["pending"]:
+                        ev0, s0 = ge["pending"].pop(0)
+                        ev0.synchronize()
+                        ge["losses"].append(float(s0[0]))
+                for ev in consumed:
+                    ev.record()
+                ge["steps"] = 3
+                for i in range(3):
+                    step_e2e_graph(i)
+                drain()
+                ge["losses"].clear()
+                ge["steps"] = args.steps
+                ms_ge, _, _, _ = timed(step_e2e_graph, args.steps, finish=drain)
+                assert len(ge["losses"]) == args.steps and all(x == x for x in ge["losses"])
+                graph_replay["e2e_ms_per_step"] = ms_ge / args.steps
+                graph_replay["no_overflow"] = graph_replay["no_overflow"] and all(p.check() for p in plans)
+        else:
+            graph_replay = {"unavailable": why}
+        del graphs
+
     e2e = None
     if not args.no_e2e:
         e2e_feed["steps"] = 3
@@ -686,6 +790,37 @@ def main() -> None:
                                   "region) + the binning totals (8 B, read when the backward starts)",
                            "api": "splatformer_b200.loader.ScenePrefetcher(" + ("loader.pack_scene(host scene)" if args.e2e_packed else "host scenes") + ") -> gs_utils.render_l1_loss(gs_params, "
                                   "cameras, images) + backward + pinned read of the loss"}
+        if graph_replay is not None:
+            if "ms_per_step" in graph_replay:
+                graph_replay["value"] = pix_step / (graph_replay["ms_per_step"] * 1e-3) / 1e6
+                graph_replay["unit"] = UNIT
+                if "e2e_ms_per_step" in graph_replay:
+                    graph_replay["e2e_value"] = pix_step / (graph_replay["e2e_ms_per_step"] * 1e-3) / 1e6
+            line["graph_replay"] = graph_replay
+            if args.headline == "graph" and graph_replay.get("no_overflow") and "value" in graph_replay:
+                # the headline is the captured step (the same kernels, launched by one graph replay per step); the
+                # eager loop's numbers stay next to it; per-kernel stage times / roofline come from the eager loop
+                # (CUDA events around every launch)
+                line["eager"] = {"value": line["value"], "ms_per_step": line["ms_per_step"]}
+                g_ms = graph_replay["ms_per_step"]
+                line["value"], line["ms_per_step"] = graph_replay["value"], g_ms
+                line["gaussians_per_s"] = scenes_per_step * V * n / (g_ms * 1e-3)
+                g_gbs = b_alg_view * v_local / (g_ms * 1e-3) / 1e9
+                line["hbm_frac_step"].update(gbs=g_gbs, frac=g_gbs / peak)
+                line["config"]["launch"] = ("one CUDA graph replay per step (splatformer_b200.graphs.capture_step "
+                                            "of render_l1_loss + backward); `eager` = the same calls uncaptured")
+                if "e2e" in line and "e2e_value" in graph_replay:
+                    line["eager"].update(e2e_value=line["e2e"]["value"], e2e_ms_per_step=line["e2e"]["ms_per_step"])
+                    line["e2e"].update(
+                        value=graph_replay["e2e_value"], ms_per_step=graph_replay["e2e_ms_per_step"],
+                        d2h_bytes_per_step=4 + 12,
+                        d2h="the step's loss (4 B, read on the host one step later, all steps inside the timed region) "
+                            "+ the binning totals (12 B into a pinned slot, checked after the loop: plan.check())",
+                        api="pinned host scene -> copy_ into the captured input tensors on a copy stream, one step "
+                            "ahead -> graph.replay() (capture_step of gs_utils.render_l1_loss + backward) -> pinned "
+                            "read of the loss")
+            else:
+                line["config"]["launch"] = "eager"
         if config3 is not None:
             line["config3"] = config3
         if other is not None:

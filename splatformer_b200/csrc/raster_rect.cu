@@ -129,7 +129,8 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
     int tiles_y, int img_w, int img_h, const int* __restrict__ view_has_isects,
     float* __restrict__ out_img, float* __restrict__ final_ts, int* __restrict__ final_idx,
     float* __restrict__ out_alpha, int clamp_rgb, const void* __restrict__ gt, int gt_u8,
-    float* __restrict__ loss_partial, int total_rects, int* __restrict__ work) {
+    float* __restrict__ loss_partial, int total_rects, int* __restrict__ work, FastDiv div_tiles,
+    FastDiv div_tiles_x) {
   __shared__ PairSlots sSlots[kRectWarps];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int tiles = tiles_x * tiles_y;
@@ -154,7 +155,7 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
   int id1 = lane < meta1.y ? __ldg(rect_ids + meta1.x + lane) : 0;
   float4 rA = nullA, rB = nullB, rC = nullA;
   if (lane < meta0.y) {
-    const int v0 = (r0 >> 3) / tiles;
+    const int v0 = fast_div(r0 >> 3, div_tiles);
     load_record_fwd(packed + ((size_t)v0 * n + __ldg(rect_ids + meta0.x + lane)) * 3, rA, rB, rC);
   }
 
@@ -169,13 +170,13 @@ __global__ void __launch_bounds__(kRectWarps * 32, SB_RECT_FWD_MINB) raster_rect
     int idn = 32 + lane < meta0.y ? __ldg(rect_ids + meta0.x + 32 + lane) : 0;
 
     const int tg = r0 >> 3, wt = r0 & 7;
-    const int v = tg / tiles, tile = tg - v * tiles;
-    const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
+    const int v = fast_div(tg, div_tiles), tile = tg - v * tiles;
+    const int tile_y = fast_div(tile, div_tiles_x), tile_x = tile - tile_y * tiles_x;
     const RectGeom rg = rect_geom(tile_x, tile_y, wt, lane, img_w, img_h);
     const int count = meta0.y;
     const int* ids = rect_ids + meta0.x;
     const float4* vp = packed + (size_t)v * n * 3;
-    const float4* vp1 = packed + (size_t)((r1 >> 3) / tiles) * n * 3;      // only used when r1 is valid
+    const float4* vp1 = packed + (size_t)fast_div(r1 >> 3, div_tiles) * n * 3;      // only used when r1 is valid
 
     float T = 1.0f, pb = 0.f;
     unsigned long long prg = pk2(0.f, 0.f);        // (red, green) accumulators, one FFMA2 per entry
@@ -399,7 +400,8 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rec
     int tiles_y, int img_w, int img_h, int clamped, const float* __restrict__ final_ts,
     const int* __restrict__ final_idx, const float* __restrict__ v_out_img,
     const float* __restrict__ v_out_alpha, const float* __restrict__ out_img,
-    const void* __restrict__ gt, int gt_u8, const float* __restrict__ v_loss, float* __restrict__ v_packed) {
+    const void* __restrict__ gt, int gt_u8, const float* __restrict__ v_loss, float* __restrict__ v_packed,
+    FastDiv div_tiles_x) {
   __shared__ SplitLists sLists[kRectWarpsB];
   __shared__ int sGid[kRectWarpsB][2][32];
   __shared__ float4 sVo[kRectWarpsB][32];
@@ -407,7 +409,7 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rec
   __shared__ float4 sRaw[kRectWarpsB][32][3];      // next chunk's raw records, filled by cp.async
   constexpr int kParts = 8 / kRectWarpsB;
   const int tile = blockIdx.x / kParts, v = blockIdx.y;
-  const int tile_y = tile / tiles_x, tile_x = tile - tile_y * tiles_x;
+  const int tile_y = fast_div(tile, div_tiles_x), tile_x = tile - tile_y * tiles_x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int wt = warp + (blockIdx.x % kParts) * kRectWarpsB;        // rectangle index within the tile
   const size_t rect = ((size_t)v * tiles_x * tiles_y + tile) * 8 + wt;
@@ -601,7 +603,7 @@ extern "C" int sb_rasterize_rect_fwd(int num_views, int n, const float* packed, 
   sb::raster_rect_fwd_kernel<<<grid, sb::kRectWarps * 32, 0, (cudaStream_t)stream>>>(
       n, reinterpret_cast<const float4*>(packed), rect_ids, reinterpret_cast<const int2*>(rect_meta), background, tiles_x,
       tiles_y, img_w, img_h, view_has_isects, out_img, final_ts, final_idx, out_alpha, clamp_rgb_max1, gt,
-      gt_is_u8, loss_partial, (int)total, work_counter);
+      gt_is_u8, loss_partial, (int)total, work_counter, sb::make_fast_div(tiles_x * tiles_y), sb::make_fast_div(tiles_x));
   SB_RETURN_LAST();
 }
 
@@ -620,6 +622,6 @@ extern "C" int sb_rasterize_rect_bwd(int num_views, int n, const float* packed, 
   sb::raster_rect_bwd_kernel<<<grid, sb::kRectWarpsB * 32, 0, (cudaStream_t)stream>>>(
       n, reinterpret_cast<const float4*>(packed), rect_ids, reinterpret_cast<const int2*>(rect_meta), background, tiles_x,
       tiles_y, img_w, img_h, clamped_rgb_max1, final_ts, final_idx, v_out_img, v_out_alpha, out_img, gt,
-      gt_is_u8, v_loss, v_packed);
+      gt_is_u8, v_loss, v_packed, sb::make_fast_div(tiles_x));
   SB_RETURN_LAST();
 }

@@ -11,6 +11,27 @@ namespace sb {
 
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+// Division of a non-negative int (< 2^31) by a fixed positive divisor with one multiply-high, one add and one shift
+// (Granlund & Montgomery, "Division by invariant integers using multiplication"): the rasterisers split a
+// rectangle number into (view, tile row, tile column) once per rectangle, three hardware-less ~20-instruction
+// divisions where the list is often empty and the rest of the rectangle's work is a few dozen instructions.
+struct FastDiv {
+  unsigned mul, shr;
+  int d;
+};
+inline FastDiv make_fast_div(int d) {
+  FastDiv f;
+  f.d = d;
+  unsigned l = 0;
+  while ((1ull << l) < (unsigned long long)d) ++l;                 // ceil(log2 d)
+  f.mul = (unsigned)(((1ull << 32) * ((1ull << l) - (unsigned long long)d)) / (unsigned long long)d + 1ull);
+  f.shr = l;
+  return f;
+}
+__device__ __forceinline__ int fast_div(int n, const FastDiv& f) {
+  return (int)(((unsigned)n + __umulhi((unsigned)n, f.mul)) >> f.shr);      // n < 2^31: the sum cannot wrap
+}
+
 // Camera of view v from the ABI's (viewmats, intrins | scalars) description.
 struct CamSrc {
   const float* viewmats;

@@ -503,10 +503,8 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rec
     acc = fmaf(fac, cdot, acc);
     const float aw = (valid && alpha_raw <= kAlphaMax) ? alpha_raw : 0.f;
     const float w = -aw * v_alpha;
-    // (the address of a step's store is the pair's base plus an immediate; the base moves once per pair, at the
-    // TOP of the pair: an add right behind the store waited for the store to have read its address register)
-    if (slot & 1) asm volatile("st.shared.v2.f32 [%0+%3], {%1, %2};" ::"r"(wcur), "f"(w), "f"(fac), "n"(kSlotStride * (int)sizeof(float2)) : "memory");
-    else asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(wcur), "f"(w), "f"(fac) : "memory");
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(wcur), "f"(w), "f"(fac) : "memory");
+    wcur += kSlotStride * (unsigned)sizeof(float2);
     if ((lane & 15) == nslot + (slot & 1)) { own_x = gx; own_y = gy; own_g = sGm[slot]; }
   };
   const unsigned lt = (1u << lane) - 1u;
@@ -542,7 +540,6 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rec
     if (c > 0) fetch(g_cur);
     if (c > 1) g_nxt = __ldg(ids + 32 * (c - 2) + lane);
     for (int j = 0; j < npairs; ++j) {
-      wcur = wbase + (unsigned)nslot * (kSlotStride * (unsigned)sizeof(float2));      // this pair's parking slots
       const float4 Q0 = my.q0[j], Q1 = my.q1[j], Q2 = my.q2[j];
       const unsigned long long dx2 = sub2(pk2(Q0.x, Q0.y), px2), dy2 = sub2(pk2(Q0.z, Q0.w), py2);
       const unsigned long long t2 = fma2(pk2(Q1.z, Q1.w), dy2, mul2(pk2(Q1.x, Q1.y), dx2));
@@ -560,6 +557,7 @@ __global__ void __launch_bounds__(kRectWarpsB * 32, SB_RECT_BWD_MINB) raster_rec
       if (nslot == kSlots) {
         flush_half_slots(sW[warp], sVo[warp], kSlots, lane, own_x, own_y, own_g, ox, oy, vgrad);
         nslot = 0;
+        wcur = wbase;
       }
     }
   }

@@ -21,6 +21,43 @@ from torch import Tensor
 Scene = Tuple[Dict[str, Tensor], Dict[str, Tensor], Optional[Tensor]]      # (gs_params, cameras, target images)
 
 
+def _parse_cpulist(text: str):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def bind_host_to_gpu(device_index: int) -> Dict[str, Any]:
+    """Binds the calling process to the CPUs next to GPU `device_index` (the PCI device's `local_cpulist` in sysfs),
+    so that the pinned staging buffers it allocates AFTERWARDS are first-touched on that GPU's NUMA node and the
+    uploads do not cross the socket interconnect.  With one process per GPU and every rank uploading a scene per
+    step, all ranks otherwise tend to draw from one socket's memory.  Call it before the first pinned allocation.
+    Best effort: returns what it did ({"bound": False, "why": ...} where sysfs says nothing useful)."""
+    import os
+    try:
+        props = torch.cuda.get_device_properties(device_index)
+        addr = f"{getattr(props, 'pci_domain_id', 0):04x}:{props.pci_bus_id:02x}:{props.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{addr}"
+        cpus = _parse_cpulist(open(f"{base}/local_cpulist").read())
+        try:
+            node = int(open(f"{base}/numa_node").read())
+        except Exception:                              # noqa: BLE001
+            node = -1
+        allowed = os.sched_getaffinity(0)
+        want = cpus & allowed
+        if not want or want == allowed:
+            return {"bound": False, "why": "the GPU's local CPU list is the whole allowed set", "pci": addr,
+                    "numa_node": node}
+        os.sched_setaffinity(0, want)
+        return {"bound": True, "pci": addr, "numa_node": node, "cpus": len(want)}
+    except Exception as e:                             # noqa: BLE001
+        return {"bound": False, "why": f"{type(e).__name__}: {e}"}
+
+
 def _upload(x: Any, device: torch.device):
     if isinstance(x, Tensor):
         return x.to(device, non_blocking=True)

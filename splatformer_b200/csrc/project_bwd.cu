@@ -136,7 +136,7 @@ __host__ __device__ inline size_t views_bwd_smem_bytes(int k3_store, bool sh, in
 
 template <int DEG>
 #ifndef SB_PROJ_BWD_MINB
-#define SB_PROJ_BWD_MINB 4
+#define SB_PROJ_BWD_MINB 5        // 96 registers, no spills: 0.170 ms (4: 128 regs 0.175, 3: 0.191, 6: 80 regs with spills)
 #endif
 __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_project_bwd_kernel(
     int num_views, int n, const float* __restrict__ means, const float* __restrict__ scales, float glob,

@@ -328,15 +328,73 @@ def run_config3(args, steps, rank, world, dev, timed, V, H, W, n):
     out["view_sharded"]["grad_rel_l2_per_tensor"] = per
     if not (worst <= 1e-4):          # also true for NaN / inf
         raise SystemExit(f"view-sharded gradients differ from the single-GPU ones: rel L2 {worst:.3e} ({per})")
+    # (the autograd graphs of the check above must be gone before anything is captured: an AccumulateGrad node kept
+    # alive from an eager pass on the default stream makes the captured backward synchronise with that stream, which
+    # invalidates the capture)
+    del routed, l1, l1f
     if args.graphs:
-        # Not attempted: an NCCL all-reduce issued while the stream is being captured invalidates the capture
-        # (cudaErrorStreamCaptureInvalidated) with the async work handle, and the blocking form hung a 2-rank
-        # capture on this stack (torch 2.11 / NCCL 2.28.9) until the box's limit.  The scene-sharded step, which
-        # has no collective, is captured above; the view-sharded step's renders alone capture and replay
-        # correctly (2 ranks, round 2: gradients within 2e-6 rel. of the eager step, no overflow).
-        out["view_sharded"]["graph_replay"] = {
-            "unavailable": "NCCL all-reduce inside stream capture invalidates the capture (async handle) or hangs "
-                           "(blocking) on this stack; not attempted, the scene-sharded step is the captured one"}
+        # One graph per scene holds the rank's render + backward; the all-reduce of the scene's flat gradient buffer
+        # is issued between replays (NCCL's stream, under the next scene's replay).  At 4-8 ranks the eager loop is
+        # host-bound (a pass renders 4-8 views: 0.3-0.5 ms of kernels behind ~0.6 ms of Python and launches).
+        plans_g = [render.RenderPlan() for _ in range(S)]
+
+        def scene_fn(i):
+            def fn(_):
+                raw_i, cams_i, gt_i = scenes[i]
+                for p in raw_i.values():
+                    p.grad = None
+                l1_i, _ = gs_utils.render_l1_loss(raw_i, cams_i, gt_i, plan=plans_g[i])
+                (l1_i.sum() * inv_views).backward()
+            return fn
+        graphs_v, why_v = [], None
+        for i in range(S):
+            fn = scene_fn(i)
+            for _ in range(2):
+                fn(0)
+            g_i, why_v = capture_step(fn, plans_g[i], 1)
+            if g_i is None:
+                break
+            graphs_v.append(g_i)
+        ok_all = torch.tensor([1 if len(graphs_v) == S else 0], device=dev)
+        dist.all_reduce(ok_all, op=dist.ReduceOp.MIN)
+        if int(ok_all.item()) == 1:
+            for g_i in graphs_v:
+                g_i.replay()
+            flats = [sbdist.flat_grad_buffer(scenes[i][0]) for i in range(S)]
+            if all(f is not None for f in flats):
+                def step_view_graph(_):
+                    for i in range(S):
+                        graphs_v[i].replay()
+                        sbdist.allreduce_flat(flats[i], overlap=True)
+                    sbdist.wait_pending()
+                for i in range(2):
+                    step_view_graph(i)
+                ms_vg, _, _, _ = timed(step_view_graph, steps)
+                ok = all(p.check() for p in plans_g)
+                # the graph path's gradients of scene 0 against all its views on one GPU
+                per_g = {}
+                for k in raw:
+                    a, b = scenes[0][0][k].grad.double(), full_raw[k].grad.double()
+                    fin = bool(torch.isfinite(a).all())
+                    per_g[k] = float((a - b).norm() / b.norm().clamp_min(1e-30)) if fin else float("inf")
+                tg = torch.tensor([max(per_g.values())], device=dev, dtype=torch.float64)
+                dist.all_reduce(tg, op=dist.ReduceOp.MAX)
+                if not (float(tg.item()) <= 1e-4):
+                    raise SystemExit(f"view-sharded graph replay: gradients differ from the single-GPU ones: {per_g}")
+                out["view_sharded"]["graph_replay"] = {
+                    "value": pix_step / (ms_vg / steps * 1e-3) / 1e6, "ms_per_step": ms_vg / steps, "no_overflow": ok,
+                    "grad_rel_l2_vs_single_gpu": float(tg.item()),
+                    "how": "one CUDA graph per scene (render + backward of the rank's views); the in-place NCCL "
+                           "all-reduce of the scene's flat gradient buffer is issued between replays, on NCCL's "
+                           "stream under the next scene's replay (dist.allreduce_flat), joined at the end of the step"}
+            else:
+                out["view_sharded"]["graph_replay"] = {"unavailable": "gradients are not one flat buffer"}
+        else:
+            out["view_sharded"]["graph_replay"] = {"unavailable": why_v or "capture failed on another rank"}
+        del graphs_v
+        # (An NCCL all-reduce INSIDE the capture is not attempted: with the async work handle it invalidates the
+        # capture -- cudaErrorStreamCaptureInvalidated -- and the blocking form hung a 2-rank capture on this stack,
+        # torch 2.11 / NCCL 2.28.9, until the box's limit.)
     return out
 
 

@@ -117,6 +117,30 @@ def _as_one_buffer(grads: Sequence[Tensor]):
     return flat
 
 
+def flat_grad_buffer(params: Dict[str, Tensor]):
+    """The one flat tensor that spans the `.grad` fields of the per-Gaussian parameters when they are blocks of a
+    single allocation (what the fused render's backward produces, render.grad_layout); None otherwise."""
+    grads = [params[k].grad for k in GRAD_KEYS if k in params and params[k].requires_grad]
+    if not grads or any(g is None for g in grads):
+        return None
+    return _as_one_buffer(grads)
+
+
+def allreduce_flat(flat: Tensor, group=None, overlap: bool = False) -> None:
+    """In-place sum over the ranks of a flat gradient buffer (flat_grad_buffer).  For steps whose render + backward
+    is replayed from a CUDA graph (graphs.capture_step): a collective cannot live inside the capture, so the graph
+    holds the render alone and the exchange is issued between replays -- on NCCL's stream, under the next scene's
+    replay when overlap=True (join with wait_pending() before the gradients are read or the same graph is replayed
+    again: its backward rewrites this buffer)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group, async_op=True)
+    if overlap:
+        _pending.append((work, flat))
+    else:
+        work.wait()
+
+
 class SyncGaussianGrads(torch.autograd.Function):
     """y_i = x_i in the forward; in the backward the incoming gradients are summed over the ranks of `group`
     with ONE all-reduce.  Usage (view-sharded scene): params = SyncGaussianGrads.apply(group, overlap, *params)

@@ -144,6 +144,24 @@ def _sync_worker(rank, world, port, out_dir):
                 assert torch.all(params[kk].grad == want), (kk, overlap)
                 # in place on the render's buffer: the leaf gradient is a block of it, nothing was packed
                 assert params[kk].grad.untyped_storage().data_ptr() == FlatGrads.flat.untyped_storage().data_ptr()
+        # the exchange issued OUTSIDE autograd (steps replayed from a CUDA graph): the flat buffer behind the
+        # .grad fields is found again and reduced in place
+        for overlap in (False, True):
+            for p in params.values():
+                p.grad = None
+            keys = ("means", "scales", "quats", "opacities", "features_dc", "features_rest")
+            FlatGrads.apply(*[params[kk] for kk in keys]).backward()
+            flat = sbdist.flat_grad_buffer(params)
+            assert flat is not None and flat.untyped_storage().data_ptr() == FlatGrads.flat.untyped_storage().data_ptr()
+            assert flat.numel() == sum(p.numel() for p in params.values())
+            sbdist.allreduce_flat(flat, overlap=overlap)
+            assert sbdist.wait_pending() == (1 if overlap else 0)
+            for i, kk in enumerate(keys):
+                assert torch.all(params[kk].grad == float(i + 1) * sum(r + 1 for r in range(world))), (kk, overlap)
+        # separate allocations have no flat buffer
+        for p in params.values():
+            p.grad = torch.ones_like(p)
+        assert sbdist.flat_grad_buffer(params) is None
         # generic fallback: gradients that are separate allocations
         for p in params.values():
             p.grad = None

@@ -56,8 +56,16 @@ constexpr int kViewsBlock = 128;
 constexpr int kViewLanes = 4;                          // threads that share one Gaussian, each taking V/4 views
 constexpr int kViewsRows = kViewsBlock / kViewLanes;   // Gaussians per block
 
+// Shared-memory row stride of a Gaussian's SH coefficients: a multiple of four floats (16-byte loads) whose quarter
+// is odd, so that the eight Gaussians of a warp (four lanes each, same address within a Gaussian) hit eight different
+// 16-byte bank groups.
+__host__ __device__ inline int fwd_sh_row(int k3) {
+  const int r = (k3 + 3) & ~3;
+  return (r & 7) ? r : r + 4;
+}
+
 #ifndef SB_PROJ_FWD_MINB
-#define SB_PROJ_FWD_MINB 4        // 128 registers: 0.211 ms vs 0.219 ms unbounded (156 registers) at the benchmark shape
+#define SB_PROJ_FWD_MINB 5        // 96 registers, no spills, with the SH coefficients read from shared memory: 0.191 ms (4: 115 regs 0.200; 6: 80 regs + spills 0.220)
 #endif
 #define SB_PROJ_FWD_BOUNDS __launch_bounds__(kViewsBlock, SB_PROJ_FWD_MINB)
 template <int DEG>
@@ -74,9 +82,13 @@ __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
   const int g0 = blockIdx.x * kViewsRows;
   const int nb = min(kViewsRows, n - g0);
   const int rowi = threadIdx.x / kViewLanes, sub = threadIdx.x % kViewLanes;
-  float c[KU * 3];
+  // SH coefficients: they STAY in shared memory and are read, four at a time, where a view's colour is evaluated.
+  // Holding the 48 floats of a degree-3 Gaussian in registers across the view loop was what pinned the kernel at 128
+  // registers (four CTAs per SM, part of the array in local memory anyway) -- and this kernel is bound by latency,
+  // not by issue slots.
+  float c[3] = {0.f, 0.f, 0.f};           // DEG < 0: the colour itself
   if (DEG >= 0) {
-    const int row = padded_row(k3_store);
+    const int row = fwd_sh_row(k3_store);
     if (color_rest) {
       stage_rows_in(smem, color_src + (size_t)g0 * 3, nb, 3, kViewsBlock, row, 0);
       if (k3_store > 3) stage_rows_in(smem, color_rest + (size_t)g0 * (k3_store - 3), nb, k3_store - 3, kViewsBlock, row, 3);
@@ -87,18 +99,15 @@ __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
   }
   // cameras: built once per block (shared memory after the SH staging rows) when there are few enough views
   const bool cams_staged = num_views <= kMaxStagedCams;
-  float* s_cams = smem + (DEG >= 0 ? kViewsRows * padded_row(k3_store) : 0);
+  float* s_cams = smem + (DEG >= 0 ? kViewsRows * fwd_sh_row(k3_store) : 0);
   if (cams_staged) {
     stage_cams(cams, campos, num_views, img_w, img_h, s_cams);
     __syncthreads();
   }
   const int g = g0 + rowi;
   if (rowi >= nb) return;
-  if (DEG >= 0) {
-    const int row = padded_row(k3_store);
-#pragma unroll
-    for (int i = 0; i < KU * 3; ++i) c[i] = smem[rowi * row + i];
-  } else {
+  const float4* crow4 = reinterpret_cast<const float4*>(smem + rowi * fwd_sh_row(k3_store));
+  if (DEG < 0) {
     c[0] = __ldg(color_src + 3 * g); c[1] = __ldg(color_src + 3 * g + 1); c[2] = __ldg(color_src + 3 * g + 2);
     if (flags & kFlagColorSigmoid) { c[0] = sigmoidf_(c[0]); c[1] = sigmoidf_(c[1]); c[2] = sigmoidf_(c[2]); }
   }
@@ -192,8 +201,20 @@ __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
       else load_campos(cams, campos, v, cp);
       sh_basis(DEG, m[0] - cp[0], m[1] - cp[1], m[2] - cp[2], Y);
       r = 0.f; gg = 0.f; b = 0.f;
+      // coefficient e = 3 k + channel; per channel the sum runs over ascending k, as it always did
 #pragma unroll
-      for (int k = 0; k < KU; ++k) { r += Y[k] * c[3 * k]; gg += Y[k] * c[3 * k + 1]; b += Y[k] * c[3 * k + 2]; }
+      for (int q4 = 0; q4 < (KU * 3 + 3) / 4; ++q4) {
+        const float4 cc = crow4[q4];
+        const float vals[4] = {cc.x, cc.y, cc.z, cc.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int e = 4 * q4 + j;
+          if (e < KU * 3) {
+            const float t = Y[e / 3] * vals[j];
+            if (e % 3 == 0) r += t; else if (e % 3 == 1) gg += t; else b += t;
+          }
+        }
+      }
       r = fmaxf(r + 0.5f, 0.f); gg = fmaxf(gg + 0.5f, 0.f); b = fmaxf(b + 0.5f, 0.f);
     } else {
       r = c[0]; gg = c[1]; b = c[2];
@@ -246,7 +267,7 @@ extern "C" int sb_views_project_fwd(int num_views, int n, const float* means, co
   sb::CamSrc cams{viewmats, viewmat_stride, intrins, fx, fy, cx, cy, c2w ? 1 : 0,
                   (flags & sb::kFlagIntrinsShared) ? 1 : 0};
   const int k3 = sh_degree < 0 ? 3 : (sh_degree + 1) * (sh_degree + 1) * 3;
-  const size_t smem = (sh_degree < 0 ? 0 : (size_t)sb::kViewsRows * (k3 | 1) * sizeof(float)) +
+  const size_t smem = (sh_degree < 0 ? 0 : (size_t)sb::kViewsRows * sb::fwd_sh_row(k3) * sizeof(float)) +
                       (num_views <= sb::kMaxStagedCams ? (size_t)num_views * sb::kCamFloats * sizeof(float) : 0);
   dim3 grid(sb::ceil_div(n, sb::kViewsRows));
   cudaStream_t st = (cudaStream_t)stream;

@@ -254,7 +254,9 @@ SB_API int sb_sort_tiles(int num_views, int tiles_per_view, int tile_capacity, c
  * int, zero-filled), sb_sort_tiles additionally writes, for every rectangle, the depth-ordered ids of the
  * Gaussians whose {alpha >= 1/255} region reaches it (exact ellipse / rectangle test on the packed records,
  * conservatively inflated) into the pool: rect_meta[rect] = (start, count), the list is
- * rect_ids[start .. start + count).  A tile claims room for its eight lists with one atomic on *pool_head;
+ * rect_ids[start .. start + count); the eight rectangles of a tile without any Gaussian get (-1, 0), which lets
+ * sb_rasterize_rect_fwd write such a tile in one go (its loss sums then sit in rectangle 0's entry of
+ * loss_partial, zeros in the other seven).  A tile claims room for its eight lists with one atomic on *pool_head;
  * if the pool runs out, bit 1 (value 2) of totals[1] is set, the tile's lists are left empty and *pool_head
  * keeps counting, so that it reports the capacity the scene needs (gaussian_ids_sorted may be NULL when only
  * the rect lists are wanted).  The two kernels below give each rectangle to one warp,

@@ -75,7 +75,8 @@ __global__ void __launch_bounds__(kSortBlock, SB_SORT_MINB) sort_tiles_kernel(in
     if (count > cap) atomicOr(totals + 1, 1);
   }
   if (len <= 0) {
-    if (rect_meta && threadIdx.x < 8) rect_meta[(size_t)blockIdx.x * 8 + threadIdx.x] = make_int2(0, 0);
+    // (start = -1: "the whole tile is empty" -- the forward rasteriser then writes the tile in one go)
+    if (rect_meta && threadIdx.x < 8) rect_meta[(size_t)blockIdx.x * 8 + threadIdx.x] = make_int2(-1, 0);
     return;
   }
   const unsigned long long* src = keys + range.x;

@@ -275,9 +275,10 @@ __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_projec
           sh_basis(DEG, m[0] - cp[0], m[1] - cp[1], m[2] - cp[2], Y);
 #pragma unroll
           for (int j = 0; j < KU; ++j) {
-            s_priv[(3 * j) * kViewsBwdBlock] += Y[j] * vr;
-            s_priv[(3 * j + 1) * kViewsBwdBlock] += Y[j] * vg;
-            s_priv[(3 * j + 2) * kViewsBwdBlock] += Y[j] * vb;
+            // (explicit FMA: gradient sums are outside the bit-exact contract of this --fmad=false unit)
+            s_priv[(3 * j) * kViewsBwdBlock] = fmaf(Y[j], vr, s_priv[(3 * j) * kViewsBwdBlock]);
+            s_priv[(3 * j + 1) * kViewsBwdBlock] = fmaf(Y[j], vg, s_priv[(3 * j + 1) * kViewsBwdBlock]);
+            s_priv[(3 * j + 2) * kViewsBwdBlock] = fmaf(Y[j], vb, s_priv[(3 * j + 2) * kViewsBwdBlock]);
           }
         } else {
           acc[0] += vr; acc[1] += vg; acc[2] += vb;

@@ -210,8 +210,11 @@ __global__ void SB_PROJ_FWD_BOUNDS views_project_fwd_kernel(
         for (int j = 0; j < 4; ++j) {
           const int e = 4 * q4 + j;
           if (e < KU * 3) {
-            const float t = Y[e / 3] * vals[j];
-            if (e % 3 == 0) r += t; else if (e % 3 == 1) gg += t; else b += t;
+            // (explicit FMA: the colour is outside the bit-exact projection / tiling contract of this
+            // --fmad=false unit, and gsplat.spherical_harmonics' own kernel, sh.cu, contracts too)
+            if (e % 3 == 0) r = fmaf(Y[e / 3], vals[j], r);
+            else if (e % 3 == 1) gg = fmaf(Y[e / 3], vals[j], gg);
+            else b = fmaf(Y[e / 3], vals[j], b);
           }
         }
       }

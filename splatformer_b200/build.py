@@ -2,9 +2,10 @@
 
     python -m splatformer_b200.build [--force] [--verbose]
 
-Every translation unit is compiled separately so that the projection kernels can be built with
-FMA contraction off (`--fmad=false`, the arithmetic contract in csrc/sb_math.cuh) while the
-rasteriser keeps FMA.  Objects go to splatformer_b200/lib/obj/, the library to
+Every translation unit is compiled separately so that the projection FORWARD can be built with
+FMA contraction off (`--fmad=false`, the arithmetic contract in csrc/sb_math.cuh: its outputs decide
+the tiling and are bit-identical to the oracle) while everything else -- the rasterisers and the
+projection backward, whose outputs are gradients -- keeps FMA.  Objects go to splatformer_b200/lib/obj/, the library to
 splatformer_b200/lib/libsplat_b200.so (git-ignored; it travels to the GPU box with gpurun).
 """
 from __future__ import annotations
@@ -31,7 +32,7 @@ UNITS = {
     "abi.cu": [],
     "sh.cu": [],
     "project_fwd.cu": ["--fmad=false"],
-    "project_bwd.cu": ["--fmad=false"],
+    "project_bwd.cu": [],
     "tiles.cu": [],
     "radix_sort.cu": [],
     "tile_sort.cu": [],

@@ -95,9 +95,12 @@ __global__ void __launch_bounds__(kProjBwdBlock) project_bwd_kernel(
 // ------------------------------------------------------------------------------------------------
 // Fused multi-view backward: counterpart of views_project_fwd_kernel.  Reads the packed gradient
 // record [M1x M1y M2xx M2xy | M2yy M0 v_r v_g | v_b ...] the raster backward accumulated for every
-// (view, Gaussian), recomputes the forward record (this TU is built with --fmad=false like the
-// forward, so `valid` is reproduced exactly) and sums the VJPs over the views in registers: four lanes
+// (view, Gaussian), recomputes the forward record and sums the VJPs over the views in registers: four lanes
 // share a Gaussian and are joined with two shuffle steps, so every gradient is written once.
+// This unit is built WITH FMA contraction (the forward, project_fwd.cu, is not: its outputs are under the bit-exact
+// tiling contract, gradients are not): 20 % fewer instructions.  The recomputed record may therefore differ from
+// the forward's in the last bit; which pairs were drawn is decided by the forward alone (a pair the rasteriser never
+// touched has an all-zero gradient record and is not walked), the recompute's own `valid` only guards the arithmetic.
 //
 // Most (view, Gaussian) records are all-zero: a Gaussian behind the opaque front of the object never
 // reaches a pixel before that pixel's transmittance runs out, and a culled one is never touched.  With
@@ -275,7 +278,6 @@ __global__ void __launch_bounds__(kViewsBwdBlock, SB_PROJ_BWD_MINB) views_projec
           sh_basis(DEG, m[0] - cp[0], m[1] - cp[1], m[2] - cp[2], Y);
 #pragma unroll
           for (int j = 0; j < KU; ++j) {
-            // (explicit FMA: gradient sums are outside the bit-exact contract of this --fmad=false unit)
             s_priv[(3 * j) * kViewsBwdBlock] = fmaf(Y[j], vr, s_priv[(3 * j) * kViewsBwdBlock]);
             s_priv[(3 * j + 1) * kViewsBwdBlock] = fmaf(Y[j], vg, s_priv[(3 * j + 1) * kViewsBwdBlock]);
             s_priv[(3 * j + 2) * kViewsBwdBlock] = fmaf(Y[j], vb, s_priv[(3 * j + 2) * kViewsBwdBlock]);
